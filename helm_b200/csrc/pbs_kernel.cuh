@@ -1,0 +1,339 @@
+// Batched programmable bootstrap (blind rotation + sample extract) for sm_100a.
+//
+// Replaces, for a whole netlist level at once, what HELM reaches one gate at a time through
+// tfhe-rs (reference src/gates.rs:255-274 -> boolean::ServerKey::{and,...}; src/gates.rs:754-785
+// -> shortint apply_lookup_table): programmable_bootstrap_lwe_ciphertext = modulus switch,
+// n sequential CMUX steps (rotate-subtract, signed gadget decomposition, (k+1)l forward folded
+// negacyclic FFTs, pointwise MAC with the Fourier BSK, (k+1) inverse FFTs, round, wrapping add)
+// and extraction of coefficient 0.
+//
+// Mapping: one CTA evaluates G gates step-synchronously so one read of BSK_i from L2 feeds G
+// external products.  The accumulator ((k+1) x N torus words per gate) and the (k+1)l spectra
+// stay in shared memory for all n steps.  The M = N/2 point complex FFT is split M = RA x RB:
+// each thread runs a whole radix-RA (then radix-RB) DFT in registers (fft_regs.cuh), with a
+// single shared-memory transpose in between (padded rows, conflict-free 128-bit accesses).
+// The twist omega^j is factored as omega^{j0} * omega^{RB j1}: the second factor is a literal,
+// the first is merged with the inter-stage twiddle into one table W(j0,k0).
+#pragma once
+#include <stdint.h>
+#include "fft_regs.cuh"
+
+namespace hb {
+
+struct PbsJob {            // one bootstrap: in = c0*src0 + c1*src1 + (cst on the body)
+    uint32_t src0, src1;   // row indices into the input array
+    int32_t c0, c1;        // small integer coefficients (0 disables the operand)
+    uint64_t cst;          // torus constant added to the body
+    uint32_t dst;          // row index into the output array
+    uint32_t tv_kind;      // 0: constant body tv_cst (boolean 1/8); 1: boxed LUT (shortint); 2: explicit body at tv_ptr
+    uint64_t tv_cst;       // kind 0: the constant; kind 1: delta
+    uint64_t lut;          // kind 1: 4 bits per table entry, entry i at bits [4i,4i+4)
+    uint32_t lut_boxes;    // kind 1: number of boxes (msg*carry)
+    uint32_t pad;
+    const void* tv_ptr;    // kind 2: N torus words (body polynomial, zero mask)
+};
+
+struct PbsArgs {
+    const void* in;   uint32_t in_stride;    // words per input row (small LWE, n+1 used)
+    void* out;        uint32_t out_stride;   // words per output row (big LWE, kN+1 used)
+    const PbsJob* jobs; uint32_t n_jobs;
+    const double2* bsk;                      // [n][ROWS][K+1][M]
+    const double2* wtab;                     // [2][M]: WA[k0*RB+j0], WB[j0*RA+k0]
+    int32_t n;  int32_t base_log;
+};
+
+template <class T> struct TorusOps;
+template <> struct TorusOps<uint32_t> {
+    static constexpr int BITS = 32;
+    __device__ static __forceinline__ uint32_t round_add(double z) {   // z in LSB units
+        return (uint32_t)__double2loint(z + 6755399441055744.0);
+    }
+};
+template <> struct TorusOps<uint64_t> {
+    static constexpr int BITS = 64;
+    __device__ static __forceinline__ uint64_t round_add(double z) {   // z in units of 2^32 LSB
+        const double magic = 6755399441055744.0;
+        const double t = z + magic;
+        const uint32_t ihi = (uint32_t)__double2loint(t);
+        const double r = t - magic;
+        const double lo = fma(z - r, 4294967296.0, magic);
+        const int32_t ilo = __double2loint(lo);
+        int64_t l64 = (int64_t)ilo;
+        if (z - r > 0.0 && ilo < 0) l64 += 4294967296ll;   // frac == +0.5 exactly: +2^31 wrapped
+        return ((uint64_t)ihi << 32) + (uint64_t)l64;
+    }
+};
+
+__device__ __forceinline__ double int2double_exact(int32_t d) {
+    return __hiloint2double(0x43300000, (int)((uint32_t)d ^ 0x80000000u)) - 4503601774854144.0;  // 2^52+2^31
+}
+
+// signed digit of level `lev` (0-based: level lev+1), tfhe-rs SignedDecomposer order (App. A.3)
+template <class T, int L> __device__ __forceinline__ int32_t digit_of(T x, int base_log, int lev) {
+    constexpr int BITS = TorusOps<T>::BITS;
+    const int tot = base_log * L;
+    T state = x;
+    if (tot < BITS) {
+        state = x >> (BITS - tot - 1);
+        state = (state + 1) >> 1;
+        state &= (((T)1) << tot) - 1;
+    }
+    const T mask = (((T)1) << base_log) - 1;
+    int32_t dig = 0;
+#pragma unroll
+    for (int l = L - 1; l >= 0; --l) {
+        if (l >= lev) {
+            T res = state & mask;
+            state >>= base_log;
+            T carry = ((res - 1) | state) & res;
+            carry >>= (base_log - 1);
+            state += carry;
+            dig = (int32_t)res - (int32_t)(carry << base_log);
+        }
+    }
+    return dig;
+}
+
+template <class T> __device__ __forceinline__ T rot_read(const T* p, int N, int c, int a) {
+    int t = c - a; if (t < 0) t += 2 * N;           // a in [0,2N)
+    return t < N ? p[t] : (T)(0 - p[t - N]);
+}
+
+template <class T> __device__ __forceinline__ T tv_body(const PbsJob& jb, int N, int idx) {
+    if (jb.tv_kind == 0) return (T)jb.tv_cst;
+    if (jb.tv_kind == 2) return reinterpret_cast<const T*>(jb.tv_ptr)[idx];
+    const int box = N / (int)jb.lut_boxes, half = box >> 1;
+    int c = idx + half; bool neg = false;
+    if (c >= N) { c -= N; neg = true; }
+    const T v = (T)((jb.lut >> (4 * (c / box))) & 15) * (T)jb.tv_cst;
+    return neg ? (T)(0 - v) : v;
+}
+
+template <class T, int N, int K, int L, int RA, int RB, int G>
+struct PbsCfg {
+    static constexpr int M = N / 2;
+    static constexpr int ROWS = (K + 1) * L;
+    static constexpr int XROW = RA * (RB + 1);
+    static constexpr int TWA = HB_TW_DEN / (4 * RA);     // omega^{RB j1} = e^{2 pi i j1 TWA/256}
+    static_assert(RA * RB == M, "FFT split");
+    static_assert(HB_TW_DEN % (4 * RA) == 0 && HB_TW_DEN % RB == 0, "twiddle table too small");
+    __host__ __device__ static constexpr size_t smem_bytes(int n) {
+        return (size_t)G * ROWS * XROW * sizeof(double2) + 2 * (size_t)M * sizeof(double2) +
+               (size_t)G * (K + 1) * N * sizeof(T) + (((size_t)G * (n + 1) * 2 + 15) & ~(size_t)15);
+    }
+};
+
+// ------------------------------------------------------------------ the kernel
+template <class T, int N, int K, int L, int RA, int RB, int G, int NT, int MINB>
+__global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
+    using C = PbsCfg<T, N, K, L, RA, RB, G>;
+    constexpr int M = C::M, ROWS = C::ROWS, XROW = C::XROW;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double2* X = reinterpret_cast<double2*>(smem_raw);                  // [G][ROWS][XROW]
+    double2* WA = X + (size_t)G * ROWS * XROW;                          // [RA][RB]  W(j0,k0) at k0*RB+j0
+    double2* WB = WA + M;                                               // [RB][RA]  W(j0,k0) at j0*RA+k0
+    T* acc = reinterpret_cast<T*>(WB + M);                              // [G][K+1][N]
+    uint16_t* atil = reinterpret_cast<uint16_t*>(acc + (size_t)G * (K + 1) * N);   // [G][n+1]
+
+    const int tid = threadIdx.x;
+    const int n = A.n;
+    const int job0 = blockIdx.x * G;
+    const T* in = reinterpret_cast<const T*>(A.in);
+
+    for (int x = tid; x < 2 * M; x += NT) WA[x] = A.wtab[x];
+    // ---- prologue: linear combination + modulus switch (App. A.5)
+    for (int g = 0; g < G; ++g) {
+        const int jid = job0 + g;
+        if (jid >= (int)A.n_jobs) { for (int x = tid; x <= n; x += NT) atil[g * (n + 1) + x] = 0; continue; }
+        const PbsJob jb = A.jobs[jid];
+        const T* s0 = in + (size_t)jb.src0 * A.in_stride;
+        const T* s1 = in + (size_t)jb.src1 * A.in_stride;
+        for (int x = tid; x <= n; x += NT) {
+            T v = 0;
+            if (jb.c0) v += (T)(int64_t)jb.c0 * s0[x];
+            if (jb.c1) v += (T)(int64_t)jb.c1 * s1[x];
+            if (x == n) v += (T)jb.cst;
+            const T sh = v >> (TorusOps<T>::BITS - ilog2c(N) - 2);
+            atil[g * (n + 1) + x] = (uint16_t)(((sh + 1) >> 1) & (2 * N - 1));
+        }
+    }
+    __syncthreads();
+    // ---- accumulator = TV * X^{-b~}
+    for (int g = 0; g < G; ++g) {
+        const int jid = job0 + g;
+        T* ag = acc + (size_t)g * (K + 1) * N;
+        if (jid >= (int)A.n_jobs) { for (int x = tid; x < (K + 1) * N; x += NT) ag[x] = 0; continue; }
+        const PbsJob jb = A.jobs[jid];
+        const int bt = atil[g * (n + 1) + n];
+        const int a0 = (2 * N - bt) & (2 * N - 1);
+        for (int x = tid; x < K * N; x += NT) ag[x] = 0;
+        for (int c = tid; c < N; c += NT) {
+            int t = c - a0; if (t < 0) t += 2 * N;
+            const T v = t < N ? tv_body<T>(jb, N, t) : (T)(0 - tv_body<T>(jb, N, t - N));
+            ag[K * N + c] = v;
+        }
+    }
+    __syncthreads();
+
+    // ---- n CMUX steps
+    for (int i = 0; i < n; ++i) {
+        int any = 0;
+#pragma unroll
+        for (int g = 0; g < G; ++g) any |= atil[g * (n + 1) + i];
+        if (any == 0) continue;                       // uniform across the CTA
+
+        // P1: rotate-subtract, decompose, twist, radix-RA DFT over j1, inter-stage twiddle
+        for (int t = tid; t < G * ROWS * RB; t += NT) {
+            const int j0 = t % RB, row = (t / RB) % ROWS, g = t / (RB * ROWS);
+            const int lev = row / (K + 1), r = row % (K + 1);
+            const int a = atil[g * (n + 1) + i];
+            const T* ap = acc + ((size_t)g * (K + 1) + r) * N;
+            double2 x[RA];
+#pragma unroll
+            for (int j1 = 0; j1 < RA; ++j1) {
+                const int c = j0 + RB * j1;
+                const T d0 = rot_read<T>(ap, N, c, a) - ap[c];
+                const T d1 = rot_read<T>(ap, N, c + M, a) - ap[c + M];
+                const double2 v = make_double2(int2double_exact(digit_of<T, L>(d0, A.base_log, lev)),
+                                               int2double_exact(digit_of<T, L>(d1, A.base_log, lev)));
+                x[j1] = cmul_tw<1>(v, j1 * C::TWA);
+            }
+            dft_regs<RA, 1>(x);
+            double2* xr = X + ((size_t)g * ROWS + row) * XROW;
+#pragma unroll
+            for (int k0 = 0; k0 < RA; ++k0) xr[k0 * (RB + 1) + j0] = cmul(x[brev<RA>(k0)], WA[k0 * RB + j0]);
+        }
+        __syncthreads();
+        // P2: radix-RB DFT over j0 (column k0), in place
+        for (int t = tid; t < G * ROWS * RA; t += NT) {
+            const int k0 = t % RA, grow = t / RA;
+            double2* xc = X + (size_t)grow * XROW + k0 * (RB + 1);
+            double2 x[RB];
+#pragma unroll
+            for (int j0 = 0; j0 < RB; ++j0) x[j0] = xc[j0];
+            dft_regs<RB, 1>(x);
+#pragma unroll
+            for (int k1 = 0; k1 < RB; ++k1) xc[k1] = x[brev<RB>(k1)];
+        }
+        __syncthreads();
+        // P3: pointwise MAC with BSK_i; one read of BSK feeds all G gates
+        for (int pos = tid; pos < M; pos += NT) {
+            const int s = (pos / RB) * (RB + 1) + (pos % RB);
+            double2 o[G][K + 1];
+#pragma unroll
+            for (int g = 0; g < G; ++g)
+#pragma unroll
+                for (int j = 0; j <= K; ++j) o[g][j] = make_double2(0.0, 0.0);
+            const double2* bp = A.bsk + (size_t)i * ROWS * (K + 1) * M + pos;
+#pragma unroll
+            for (int row = 0; row < ROWS; ++row) {
+                double2 b[K + 1];
+#pragma unroll
+                for (int j = 0; j <= K; ++j) b[j] = __ldg(bp + (size_t)(row * (K + 1) + j) * M);
+#pragma unroll
+                for (int g = 0; g < G; ++g) {
+                    const double2 f = X[((size_t)g * ROWS + row) * XROW + s];
+#pragma unroll
+                    for (int j = 0; j <= K; ++j) cfma(o[g][j], f, b[j]);
+                }
+            }
+#pragma unroll
+            for (int g = 0; g < G; ++g)
+#pragma unroll
+                for (int j = 0; j <= K; ++j) X[((size_t)g * ROWS + j) * XROW + s] = o[g][j];
+        }
+        __syncthreads();
+        // P4: inverse radix-RB DFT over k1 (column k0), conj inter-stage twiddle
+        for (int t = tid; t < G * (K + 1) * RA; t += NT) {
+            const int k0 = t % RA, j = (t / RA) % (K + 1), g = t / (RA * (K + 1));
+            double2* xc = X + ((size_t)g * ROWS + j) * XROW + k0 * (RB + 1);
+            double2 x[RB];
+#pragma unroll
+            for (int k1 = 0; k1 < RB; ++k1) x[k1] = xc[k1];
+            dft_regs<RB, -1>(x);
+#pragma unroll
+            for (int j0 = 0; j0 < RB; ++j0) xc[j0] = cmul_conj(x[brev<RB>(j0)], WB[j0 * RA + k0]);
+        }
+        __syncthreads();
+        // P5: inverse radix-RA DFT over k0, untwist, round, wrapping add into the accumulator
+        for (int t = tid; t < G * (K + 1) * RB; t += NT) {
+            const int j0 = t % RB, j = (t / RB) % (K + 1), g = t / (RB * (K + 1));
+            const double2* xr = X + ((size_t)g * ROWS + j) * XROW;
+            double2 x[RA];
+#pragma unroll
+            for (int k0 = 0; k0 < RA; ++k0) x[k0] = xr[k0 * (RB + 1) + j0];
+            dft_regs<RA, -1>(x);
+            T* ap = acc + ((size_t)g * (K + 1) + j) * N;
+#pragma unroll
+            for (int j1 = 0; j1 < RA; ++j1) {
+                const double2 z = cmul_tw<-1>(x[brev<RA>(j1)], j1 * C::TWA);
+                const int c = j0 + RB * j1;
+                ap[c] += TorusOps<T>::round_add(z.x);
+                ap[c + M] += TorusOps<T>::round_add(z.y);
+            }
+        }
+        __syncthreads();
+    }
+
+    // ---- epilogue: sample extract coefficient 0 (App. A.5)
+    T* out = reinterpret_cast<T*>(A.out);
+    for (int g = 0; g < G; ++g) {
+        const int jid = job0 + g;
+        if (jid >= (int)A.n_jobs) continue;
+        const uint32_t dst = A.jobs[jid].dst;
+        const T* ag = acc + (size_t)g * (K + 1) * N;
+        T* o = out + (size_t)dst * A.out_stride;
+        for (int x = tid; x < K * N; x += NT) {
+            const int j = x / N, c = x % N;
+            o[x] = c == 0 ? ag[j * N] : (T)(0 - ag[j * N + N - c]);
+        }
+        if (tid == 0) o[K * N] = ag[K * N];
+    }
+}
+
+// ------------------------------------------------------------------ BSK: standard -> Fourier (once per key)
+// One CTA per polynomial; same two-stage transform and the same output position order as the PBS kernel.
+// scale = 2^(32-BITS) / M folds the inverse-FFT normalisation and the torus scaling into the key.
+template <class T, int N, int RA, int RB>
+__global__ void bsk_fft_kernel(const T* __restrict__ std_bsk, double2* __restrict__ out, const double2* __restrict__ wtab, double scale) {
+    constexpr int M = N / 2, TWA = HB_TW_DEN / (4 * RA);
+    __shared__ double2 X[RA * (RB + 1)];
+    const T* p = std_bsk + (size_t)blockIdx.x * N;
+    using ST = typename std::conditional<sizeof(T) == 4, int32_t, int64_t>::type;
+    for (int j0 = threadIdx.x; j0 < RB; j0 += blockDim.x) {
+        double2 x[RA];
+#pragma unroll
+        for (int j1 = 0; j1 < RA; ++j1) {
+            const int c = j0 + RB * j1;
+            const double2 v = make_double2((double)(ST)p[c] * scale, (double)(ST)p[c + M] * scale);
+            x[j1] = cmul_tw<1>(v, j1 * TWA);
+        }
+        dft_regs<RA, 1>(x);
+#pragma unroll
+        for (int k0 = 0; k0 < RA; ++k0) X[k0 * (RB + 1) + j0] = cmul(x[brev<RA>(k0)], wtab[k0 * RB + j0]);
+    }
+    __syncthreads();
+    for (int k0 = threadIdx.x; k0 < RA; k0 += blockDim.x) {
+        double2 x[RB];
+#pragma unroll
+        for (int j0 = 0; j0 < RB; ++j0) x[j0] = X[k0 * (RB + 1) + j0];
+        dft_regs<RB, 1>(x);
+#pragma unroll
+        for (int k1 = 0; k1 < RB; ++k1) out[(size_t)blockIdx.x * M + k0 * RB + k1] = x[brev<RB>(k1)];
+    }
+}
+
+// W(j0,k0) = e^{2 pi i j0 (4 k0 + 1) / (4M)} in both access orders
+__global__ void wtab_kernel(double2* wtab, int RA, int RB) {
+    const int M = RA * RB;
+    for (int x = blockIdx.x * blockDim.x + threadIdx.x; x < M; x += gridDim.x * blockDim.x) {
+        const int k0 = x / RB, j0 = x % RB;
+        const long num = ((long)j0 * (4 * k0 + 1)) % (4L * M);
+        double s, c;
+        sincospi((double)num / (double)(2 * M), &s, &c);
+        wtab[k0 * RB + j0] = make_double2(c, s);
+        wtab[M + j0 * RA + k0] = make_double2(c, s);
+    }
+}
+
+}  // namespace hb

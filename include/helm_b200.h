@@ -1,0 +1,111 @@
+/*
+ * helm_b200.h -- C ABI of the B200-native batched TFHE bootstrapping engine behind HELM's
+ * gate / LUT evaluation.  Plain pointers and sizes only; no exceptions cross the boundary.
+ *
+ * What each entry point replaces in the reference (TrustworthyComputing/helm @ fc9f75f):
+ *   hb_ctx_create / hb_set_params / hb_load_bsk / hb_load_ksk
+ *        key conversion done once per run: src/bin/helm.rs:187-192 (convert_lwe_bootstrap_key,
+ *        convert_lwe_keyswitch_key on the reference's own GPU path) and the ServerKey built by
+ *        gen_keys(), src/bin/helm.rs:241 / :301.
+ *   hb_wires_*   the wire map HashMap<String, Arc<RwLock<Ciphertext>>> of
+ *        src/circuit.rs:517-520 (and the per-level H2D/D2H staging of src/circuit.rs:745-761,
+ *        877-892, which disappears: wires stay resident in HBM between levels).
+ *   hb_eval_level   one iteration of the level loop, src/circuit.rs:524-543 (gates.par_iter_mut()
+ *        calling Gate::evaluate_encrypted, src/gates.rs:241-280; LUT mode src/circuit.rs:1050-1077
+ *        calling lut(), src/gates.rs:754-785) -- the reference's precedent for this batched shape
+ *        is discard_<gate>_lwe_ciphertext_vector(out, in1, in2, bsk, ksk), src/circuit.rs:807-873.
+ *   hb_pbs_batch / hb_keyswitch_batch   the two tfhe-rs primitives underneath
+ *        (programmable_bootstrap_lwe_ciphertext, keyswitch_lwe_ciphertext).
+ *
+ * Threading: one hb_ctx is bound to one CUDA device and driven by one host thread at a time;
+ * work is stream-ordered on the context's stream.  Host buffers are only read/written during the
+ * call.  The engine never sees a secret key.
+ * There is no CPU fallback: every compute entry point returns HB_ERR_CUDA when no device exists.
+ */
+#ifndef HELM_B200_H
+#define HELM_B200_H
+#include <stdint.h>
+#include <stddef.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef int32_t hb_status;
+enum { HB_OK = 0, HB_ERR_ARG = 1, HB_ERR_CUDA = 2, HB_ERR_STATE = 3, HB_ERR_UNSUPPORTED = 4 };
+
+typedef struct hb_ctx hb_ctx;
+typedef struct hb_wires hb_wires;
+
+typedef struct {
+    int32_t n, k, N;                    /* small LWE dim, GLWE dim, polynomial size */
+    int32_t pbs_base_log, pbs_level;
+    int32_t ks_base_log, ks_level;
+    int32_t torus_bits;                 /* 32 | 64 */
+    int32_t order;                      /* 0 = PBS then KS (boolean; wires under the small key)
+                                           1 = KS then PBS (shortint; wires under the big key) */
+    int32_t msg_mod, carry_mod;         /* shortint only */
+} hb_params;
+
+/* gate opcodes (GateType of src/gates.rs:23-45 that reach the FHE library) */
+enum { HB_AND = 0, HB_NAND, HB_OR, HB_NOR, HB_XOR, HB_XNOR, HB_MUX, HB_NOT, HB_COPY, HB_LUT };
+
+typedef struct {
+    uint8_t op;          /* HB_* */
+    uint8_t arity;       /* LUT: number of inputs (1..4) */
+    uint16_t flags;
+    uint32_t in[4];      /* wire indices; MUX: in[0]=then, in[1]=else, in[2]=select (src/gates.rs:265) */
+    uint32_t out;        /* wire index */
+    uint64_t lut;        /* LUT: truth table, bit i = output for index i; index = sum in[j] << (arity-1-j)
+                            (first input is the MSB, src/gates.rs:158-181) */
+} hb_gate;
+
+typedef struct {
+    uint64_t pbs_count, ks_count, levels;
+    double pbs_ms, ks_ms;               /* device time of the last hb_eval_level / batch call */
+    uint64_t kernel_launches;           /* engine kernels launched since context creation */
+} hb_stats_t;
+
+hb_status hb_ctx_create(int32_t device, hb_ctx** out);
+hb_status hb_ctx_destroy(hb_ctx*);
+const char* hb_last_error(const hb_ctx*);          /* ctx may be NULL: last creation error */
+hb_status hb_set_params(hb_ctx*, const hb_params*);
+/* standard-domain GGSW list, layout [n][level 1..l][row 0..k][poly 0..k][N]; transformed once, resident */
+hb_status hb_load_bsk(hb_ctx*, const void* bsk, size_t bytes);
+/* layout [kN][level 1..l_ks][n+1]; resident */
+hb_status hb_load_ksk(hb_ctx*, const void* ksk, size_t bytes);
+
+/* device-resident wire array [n_wires][stride]; ciphertext words = n+1 (order 0) or kN+1 (order 1) */
+hb_status hb_wires_create(hb_ctx*, uint32_t n_wires, hb_wires** out);
+/* wrap caller-owned device memory (e.g. a torch tensor used for the per-level NCCL all-gather) */
+hb_status hb_wires_attach(hb_ctx*, void* device_ptr, uint32_t n_wires, hb_wires** out);
+hb_status hb_wires_destroy(hb_wires*);
+uint32_t hb_ct_words(const hb_ctx*);                /* words per ciphertext on the wire */
+uint32_t hb_wire_stride(const hb_ctx*);             /* words per wire row in device memory */
+void* hb_wires_device_ptr(hb_wires*);
+/* host <-> device: packed rows of hb_ct_words() torus words */
+hb_status hb_wires_write(hb_wires*, const uint32_t* idx, uint32_t cnt, const void* lwe_host);
+hb_status hb_wires_read(hb_wires*, const uint32_t* idx, uint32_t cnt, void* lwe_host);
+hb_status hb_wires_set_trivial(hb_wires*, const uint32_t* idx, uint32_t cnt, const uint64_t* plaintext);
+
+/* evaluate every gate of one level as one batched launch sequence (asynchronous on the ctx stream).
+ * No gate of the batch may read a wire written by another gate of the same batch. */
+hb_status hb_eval_level(hb_ctx*, hb_wires*, const hb_gate* gates, uint32_t n_gates);
+hb_status hb_sync(hb_ctx*);
+hb_status hb_stats(hb_ctx*, hb_stats_t* out);
+/* CUDA stream of the context (cudaStream_t as void*), for callers that interleave collectives */
+void* hb_stream(hb_ctx*);
+
+/* primitives on host buffers (unit parity with the oracle):
+ * lwe_in: count x (n+1); test_vector_bodies: count x N body polynomials (1 x N if shared_tv != 0; the
+ * mask polynomials of the accumulator are zero, as in every caller on this path); out: count x (kN+1) */
+hb_status hb_pbs_batch(hb_ctx*, const void* lwe_in, const void* test_vector_bodies, int32_t shared_tv,
+                       uint32_t count, void* lwe_out);
+/* lwe_in: count x (kN+1); out: count x (n+1) */
+hb_status hb_keyswitch_batch(hb_ctx*, const void* lwe_in, uint32_t count, void* lwe_out);
+/* measured FP64 FMA throughput of this device in TFLOP/s (register-resident DFMA loop) */
+hb_status hb_measure_fp64_peak(hb_ctx*, double* tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -45,8 +45,10 @@ PARAM_SETS = {
     # small set for fast CPU tests (NOT secure; same code paths, k=2 / l=3 like boolean_default)
     "toy32": dict(n=48, k=2, N=512, pbs_base_log=6, pbs_level=3, ks_base_log=3, ks_level=4,
                   torus_bits=32, order=0, msg_mod=0, carry_mod=0, lwe_std=2.0 ** -20, glwe_std=2.0 ** -28),
-    "toy64": dict(n=40, k=1, N=1024, pbs_base_log=23, pbs_level=1, ks_base_log=4, ks_level=5,
-                  torus_bits=64, order=1, msg_mod=2, carry_mod=2, lwe_std=2.0 ** -24, glwe_std=2.0 ** -50),
+    "toy64": dict(n=40, k=1, N=2048, pbs_base_log=23, pbs_level=1, ks_base_log=3, ks_level=5,
+                  torus_bits=64, order=1, msg_mod=4, carry_mod=4, lwe_std=2.0 ** -24, glwe_std=2.0 ** -52),
+    "toy64b": dict(n=36, k=3, N=512, pbs_base_log=18, pbs_level=1, ks_base_log=3, ks_level=4,
+                   torus_bits=64, order=1, msg_mod=2, carry_mod=2, lwe_std=2.0 ** -24, glwe_std=2.0 ** -42),
 }
 
 

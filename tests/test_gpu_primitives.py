@@ -1,0 +1,49 @@
+"""GPU parity of the two primitives under every gate (reference src/gates.rs:255-274 -> tfhe-rs
+programmable bootstrap + keyswitch) against the CPU oracle, through the C ABI."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+U32_SETS = ["toy32", "boolean_default"]
+
+
+@pytest.mark.parametrize("name", U32_SETS + ["toy64", "toy64b"])
+def test_keyswitch_bit_exact(name, keys_factory, engine_factory):
+    K, eng = keys_factory(name), engine_factory(name)
+    rng = np.random.default_rng(1)
+    cnt = 37      # ragged: not a multiple of the 16-gate tile
+    info = np.iinfo(K.dtype)
+    cts = rng.integers(0, info.max, size=(cnt, K.kN + 1), dtype=K.dtype, endpoint=True)
+    got = eng.keyswitch_batch(cts)
+    for i in range(cnt):
+        assert np.array_equal(got[i], K.keyswitch(cts[i])), "keyswitch row %d differs" % i
+
+
+@pytest.mark.parametrize("name", U32_SETS)
+def test_pbs_bit_exact_u32(name, keys_factory, engine_factory, oracle_mod):
+    """u32 torus: the f64 FFT external product rounds to the exact integer negacyclic product,
+    so the GPU ciphertext must be bit-identical to the oracle's exact-integer back-end."""
+    K, eng = keys_factory(name), engine_factory(name)
+    cnt = 5 if name == "boolean_default" else 9     # odd: exercises the half-filled G=2 CTA
+    cts = np.stack([K.enc_bool(i & 1, 100 + i) for i in range(cnt)])
+    tv = K.bool_tv().reshape(K.k + 1, K.N)[K.k]
+    got = eng.pbs_batch(cts, tv[None, :])
+    for i in range(cnt):
+        want = K.pbs(cts[i], K.bool_tv(), mode=oracle_mod.EXACT)
+        assert np.array_equal(got[i], want), "pbs row %d differs in %d words" % (i, np.count_nonzero(got[i] != want))
+        assert K.dec_bool(got[i], big=1) == bool(i & 1)
+
+
+def test_pbs_arbitrary_test_vector(keys_factory, engine_factory, oracle_mod):
+    K, eng = keys_factory("toy32"), engine_factory("toy32")
+    rng = np.random.default_rng(5)
+    cnt = 4
+    cts = rng.integers(0, 2 ** 32, size=(cnt, K.n + 1), dtype=np.uint64).astype(np.uint32)
+    tvb = rng.integers(0, 2 ** 32, size=(cnt, K.N), dtype=np.uint64).astype(np.uint32)
+    got = eng.pbs_batch(cts, tvb)
+    for i in range(cnt):
+        tv = np.zeros((K.k + 1, K.N), dtype=np.uint32)
+        tv[K.k] = tvb[i]
+        want = K.pbs(cts[i], tv.reshape(-1), mode=oracle_mod.EXACT)
+        assert np.array_equal(got[i], want)
