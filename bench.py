@@ -1,0 +1,377 @@
+#!/usr/bin/env python
+"""bench.py -- PBS/s of batched gate bootstraps on the synthetic levelized netlist (BASELINE.json configs[4]:
+65 536 two-input gates per level, depth 32, tfhe boolean DEFAULT_PARAMETERS), SURVEY.md section 8(d) item 5.
+
+A "step" is one netlist level: ONE hb_eval_level call = 65 536 gate bootstraps (fused linear part -> blind
+rotation -> sample extract -> keyswitch), i.e. one pass of the hot path over one batch.  Step s evaluates level
+(s mod 32)+1, reading the wires of level (s mod 32) and writing the next block of the device-resident wire array.
+With N > 1 GPUs every level is sharded across the ranks (W/N gates each; BSK/KSK replicated) and the level's
+output ciphertexts are exchanged with one NCCL all-gather before the next level ("strong" scaling: the total
+work per step is fixed).
+
+  value    device-resident throughput (inputs already in HBM), CUDA events on the engine's stream, max over ranks
+  e2e      the same levels through the C ABI with HOST buffers: hb_wires_write_rows (pinned host -> device) of the
+           level's input wires, hb_eval_level, hb_wires_read_rows of the level's outputs, all inside the timed region
+  roofline the PBS kernel: algorithmic FP64 flops per launch (141.95 MFLOP per PBS) / its CUDA-event
+           duration, against the DFMA peak measured in this run by a register-resident FMA loop
+  cpu_baseline / --impl reference: the CPU restatement of the reference's tfhe-rs path (oracle/, f64-FFT mode, one
+           gate per thread like rayon par_iter) on the host cores, on a bounded sample of the same level.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W_DEFAULT, DEPTH = 65536, 32
+PARAM_SET = "boolean_default"
+F_CMUX = 196608.0            # flops per CMUX step, boolean default
+GATE_OPS = 6                 # AND NAND OR NOR XOR XNOR
+
+
+# ---------------------------------------------------------------- deterministic workload (splitmix64)
+def splitmix64(seed, count):
+    x = (np.uint64(seed) + np.arange(1, count + 1, dtype=np.uint64) * np.uint64(0x9E3779B97F4A7C15))
+    z = x
+    z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+    z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+    return z ^ (z >> np.uint64(31))
+
+
+def synth_level(level, W):
+    """gate (level, j): two wires drawn uniformly from level-1, type uniform over the 6 two-input gates (seed 1)."""
+    r = splitmix64(1 + 1000003 * level, 3 * W)
+    in0 = (r[0::3] % np.uint64(W)).astype(np.uint32)
+    in1 = (r[1::3] % np.uint64(W)).astype(np.uint32)
+    ops = (r[2::3] % np.uint64(GATE_OPS)).astype(np.uint8)
+    return ops, in0, in1
+
+
+def plain_gate(ops, a, b):
+    a = a.astype(bool); b = b.astype(bool)
+    res = np.zeros(len(ops), dtype=bool)
+    for op, f in enumerate((a & b, ~(a & b), a | b, ~(a | b), a ^ b, ~(a ^ b))):
+        res = np.where(ops == op, f, res)
+    return res
+
+
+# ---------------------------------------------------------------- clocks sampler
+class Clocks:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(device), "--query-gpu=" + self.Q,
+                                       "--format=csv,noheader,nounits", "-lms", "200"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except OSError:
+            pass
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 6:
+                continue
+            try:
+                sm.append(float(c[0])); mx.append(float(c[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, c[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        try:
+            os.unlink(self.f.name)
+        except OSError:
+            pass
+        if sm:
+            out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                   "samples": len(sm)}
+        return out
+
+
+# ---------------------------------------------------------------- CPU arm (oracle = restated reference path)
+def cpu_level_sample(K, O, wires0, level_gates, count, mode):
+    ops, in0, in1 = level_gates
+    nw = wires0.shape[0]
+    buf = np.concatenate([wires0, np.zeros((count, wires0.shape[1]), dtype=wires0.dtype)])
+    t = time.perf_counter()
+    threads = K.bool_level(buf, ops[:count], in0[:count], in1[:count], in0[:count], nw + np.arange(count), mode=mode)
+    return time.perf_counter() - t, threads, buf[nw:]
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (restated; tfhe-rs itself cannot be built here) on the host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import oracle as O
+    K = O.Keys(PARAM_SET, seed=3)
+    W = args.width
+    bits0 = (splitmix64(2, W) & np.uint64(1)).astype(np.uint8)
+    threads = os.cpu_count() or 1
+    sample = max(threads, min(W, args.cpu_gates if args.cpu_gates else 4 * threads))
+    # only the wires the sample reads need to exist: encrypt level 0 lazily
+    times = []
+    for s in range(args.warmup + args.steps):
+        lvl = s % DEPTH + 1
+        ops, in0, in1 = synth_level(lvl, W)
+        need = np.unique(np.concatenate([in0[:sample], in1[:sample]]))
+        remap = np.zeros(W, dtype=np.uint32); remap[need] = np.arange(len(need), dtype=np.uint32)
+        w0 = K.enc_bool_batch(bits0[need], 10_000 + 7 * s)
+        dt, threads, out = cpu_level_sample(K, O, w0, (ops, remap[in0], remap[in1]), sample, O.FFT)
+        want = plain_gate(ops[:sample], bits0[in0[:sample]], bits0[in1[:sample]])
+        assert np.array_equal(K.dec_bool_batch(out), want), "reference arm: wrong gate outputs"
+        if s >= args.warmup:
+            times.append(dt)
+    tot = float(sum(times))
+    v = sample * len(times) / tot
+    line = {"impl": "reference", "metric": "PBS/s (batched gate bootstraps)", "value": v, "unit": "PBS/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / len(times),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args, 1),
+            "cpu_baseline": {"value": v, "unit": "PBS/s", "cores": threads, "kind": "port",
+                             "sample": "%d gates of the level per step (of %d), oracle f64-FFT, OpenMP one gate per thread"
+                                       % (sample, W)},
+            "e2e": {"value": v, "unit": "PBS/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def workload_config(args, n):
+    return {"workload": "synthetic levelized netlist, %d two-input gates/level, depth %d (BASELINE.json configs[4])"
+                        % (args.width, DEPTH),
+            "params": "tfhe boolean DEFAULT_PARAMETERS n=722 k=2 N=512 l=3 B=2^6 ks l=4 B=2^3 (u32 torus)",
+            "step": "one level = one hb_eval_level batch of %d gate bootstraps (PBS + keyswitch each)" % args.width,
+            "sharding": "level sharded over %d GPU(s), keys replicated, NCCL all-gather of outputs per level" % n if n > 1
+                        else "single GPU",
+            "l2": "inputs larger than L2: each level reads/writes a different 190 MB block of the 6.3 GB wire array"}
+
+
+def hbm_peak_gbs():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except Exception:
+        return 6650.0        # fallback stated in B200_PROFILING.md
+
+
+# ---------------------------------------------------------------- GPU arm
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=6)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--width", type=int, default=W_DEFAULT, help="gates per level (default: the BASELINE config, 65536)")
+    ap.add_argument("--cpu-gates", type=int, default=0, help="CPU sample size (gates); default 4 x host threads")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import helm_b200
+    from helm_b200 import engine as E
+    from oracle import oracle as O       # checker + cpu_baseline only; never on the measured GPU path
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- helm_b200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    W = args.width
+    assert W % world == 0
+    Wr = W // world
+    g0 = rank * Wr
+
+    K = O.Keys(PARAM_SET, seed=3)
+    eng = helm_b200.Engine(K.params, device=local)
+    eng.load_keys(K.bsk(), K.ksk())
+    stride, words = eng.stride, eng.ct_words
+    # device wire array: (DEPTH+1) level blocks of W rows; attached so torch/NCCL can address it
+    wt = torch.zeros(((DEPTH + 1) * W, stride), dtype=torch.int32, device="cuda")
+    wires = eng.wires((DEPTH + 1) * W, device_ptr=wt.data_ptr())
+    ext = torch.cuda.ExternalStream(eng.stream(), device=torch.device("cuda", local))
+
+    bits0 = (splitmix64(2, W) & np.uint64(1)).astype(np.uint8)
+    ct0 = K.enc_bool_batch(bits0, 1_000_000)                     # level-0 inputs, client side
+    wires.write_rows(0, ct0)
+    levels = []
+    for lvl in range(1, DEPTH + 1):
+        ops, in0, in1 = synth_level(lvl, W)
+        sl = slice(g0, g0 + Wr)
+        levels.append(E.make_gates(ops[sl], (lvl - 1) * W + in0[sl], (lvl - 1) * W + in1[sl],
+                                   lvl * W + g0 + np.arange(Wr, dtype=np.uint32)))
+
+    def exchange(lvl):
+        if world > 1:
+            blk = wt[lvl * W:(lvl + 1) * W]
+            with torch.cuda.stream(ext):
+                dist.all_gather_into_tensor(blk, blk[g0:g0 + Wr])
+
+    def step_resident(s):
+        lvl = s % DEPTH + 1
+        eng.eval_level(wires, levels[lvl - 1])
+        exchange(lvl)
+
+    def barrier():
+        eng.sync()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    fp64_peak = eng.fp64_peak_tflops()
+
+    # ---- device-resident timing
+    for s in range(args.warmup):
+        step_resident(s)
+    barrier()
+    st0 = eng.stats()
+    clk = Clocks(local) if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(ext)
+    for s in range(args.warmup, args.warmup + args.steps):
+        step_resident(s)
+    e1.record(ext)
+    barrier()
+    clocks = clk.stop() if clk else None
+    st1 = eng.stats()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    launches = int(st1["kernel_launches"] - st0["kernel_launches"])
+    pbs_ms = (st1["pbs_ms_total"] - st0["pbs_ms_total"]) / args.steps
+    ks_ms = (st1["ks_ms_total"] - st0["ks_ms_total"]) / args.steps
+
+    # ---- correctness of what was just timed: replay the netlist in plaintext and decrypt a sample of the last level
+    nsteps = args.warmup + args.steps
+    last = (nsteps - 1) % DEPTH + 1
+    verified = None
+    if nsteps <= DEPTH or True:
+        cur = bits0.astype(bool)
+        plain = {0: cur}
+        for lvl in range(1, min(nsteps, DEPTH) + 1):
+            ops, in0, in1 = synth_level(lvl, W)
+            cur = plain_gate(ops, cur[in0], cur[in1])
+            plain[lvl] = cur
+        if last in plain:
+            ns = min(Wr, 2048)
+            got = np.zeros((ns, words), dtype=eng.dtype)
+            wires.read_rows(last * W + g0, got)
+            dec = K.dec_bool_batch(got)
+            verified = bool(np.array_equal(dec, plain[last][g0:g0 + ns]))
+            if not verified:
+                raise SystemExit("bench.py: decrypted outputs of level %d differ from the plaintext netlist" % last)
+
+    # ---- end to end through the C ABI with host buffers (pinned), copies inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        hin = torch.empty((W, words), dtype=torch.int32).pin_memory()
+        hout = torch.empty((Wr, words), dtype=torch.int32).pin_memory()
+        hin_np = hin.numpy().view(eng.dtype); hout_np = hout.numpy().view(eng.dtype)
+        hin_np[:] = ct0
+
+        def step_e2e(s):
+            lvl = s % DEPTH + 1
+            wires.write_rows((lvl - 1) * W, hin_np)            # H2D: the level's input wires (host -> HBM)
+            eng.eval_level(wires, levels[lvl - 1])
+            wires.read_rows(lvl * W + g0, hout_np)             # D2H: this rank's output ciphertexts (syncs)
+        for s in range(args.warmup):
+            step_e2e(0)
+        barrier()
+        t0 = time.perf_counter()
+        e0.record(ext)
+        for s in range(args.steps):
+            step_e2e(0)
+        e1.record(ext)
+        barrier()
+        wall = (time.perf_counter() - t0) * 1e3
+        t = torch.tensor([max(e0.elapsed_time(e1), wall)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ops1, i0, i1 = synth_level(1, W)
+        ns = min(Wr, 1024)
+        ok = np.array_equal(K.dec_bool_batch(hout_np[:ns]), plain_gate(ops1, bits0[i0], bits0[i1])[g0:g0 + ns])
+        if not ok:
+            raise SystemExit("bench.py: e2e outputs decrypt wrong")
+        e2e = {"value": W * args.steps / (float(t.item()) * 1e-3), "unit": "PBS/s",
+               "h2d_bytes_per_step": int(hin_np.nbytes + levels[0].nbytes), "d2h_bytes_per_step": int(hout_np.nbytes),
+               "ms_per_step": float(t.item()) / args.steps}
+
+    # ---- CPU baseline (rank 0, N = 1 only): bounded sample of level 1 on the host cores
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        threads = os.cpu_count() or 1
+        sample = args.cpu_gates if args.cpu_gates else 4 * threads
+        ops1, i0, i1 = synth_level(1, W)
+        need = np.unique(np.concatenate([i0[:sample], i1[:sample]]))
+        remap = np.zeros(W, dtype=np.uint32); remap[need] = np.arange(len(need), dtype=np.uint32)
+        cpu_level_sample(K, O, ct0[need], (ops1, remap[i0], remap[i1]), min(sample, threads), O.FFT)   # warm (Fourier BSK)
+        dt, threads, out = cpu_level_sample(K, O, ct0[need], (ops1, remap[i0], remap[i1]), sample, O.FFT)
+        gpu = np.zeros((sample, words), dtype=eng.dtype)
+        wires.write_rows(0, ct0)
+        eng.eval_level(wires, levels[0]); eng.sync()
+        wires.read_rows(W, gpu)
+        same_bits = bool(np.array_equal(K.dec_bool_batch(out), K.dec_bool_batch(gpu)))
+        cpu = {"value": sample / dt, "unit": "PBS/s", "cores": int(threads), "kind": "port",
+               "sample": "%d gates of level 1 (of %d), oracle f64-FFT mode, OpenMP one gate per thread; %.1f s; "
+                         "decrypts identical to the GPU outputs: %s" % (sample, W, dt, same_bits)}
+
+    if rank == 0:
+        value = W * args.steps / (ms_total * 1e-3)
+        flops_per_launch = Wr * K.n * F_CMUX
+        ach = flops_per_launch / (pbs_ms * 1e-3) / 1e12 if pbs_ms > 0 else None
+        bsk_bytes = K.n * 9 * 3 * 256 * 16
+        line = {"metric": "PBS/s (batched gate bootstraps)", "value": value, "unit": "PBS/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic", "config": workload_config(args, world),
+                "roofline": {"bound": "fp64", "kernel": "pbs_kernel<u32,N=512,k=2,l=3> (blind rotation)",
+                             "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s",
+                             "frac": (ach / fp64_peak) if ach else None, "traffic": None,
+                             "peak_source": "measured in this run: register-resident DFMA loop (hb_measure_fp64_peak); "
+                                            "MEASURED_PEAKS.json has no FP64 entry",
+                             "flops_per_launch": flops_per_launch, "kernel_ms": pbs_ms, "ks_kernel_ms": ks_ms,
+                             "hbm_floor_ms": 1e3 * (bsk_bytes + 3.0 * Wr * words * 4) / (hbm_peak_gbs() * 1e9)},
+                "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+                "verified": verified}
+        print(json.dumps(line))
+    wires.close()
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -167,11 +167,26 @@ int find_shape(const hb_params& p) {
 namespace {
 
 constexpr int NSLOT = 4;
-struct JobSlot { PinBuf pin; DevBuf dev; cudaEvent_t done = nullptr; };
+struct JobSlot {
+    PinBuf pin; DevBuf dev; cudaEvent_t done = nullptr;
+    cudaEvent_t t[3] = {nullptr, nullptr, nullptr};   // brackets of the two phases of one level
+    bool pending = false; int first_is_pbs = 1;
+};
 struct CtxExtra { JobSlot slots[NSLOT]; uint64_t next = 0; };
 // kept outside hb_ctx's public-ish layout; one per context
 std::vector<std::pair<hb_ctx*, CtxExtra*>> g_extra;
 CtxExtra* extra_of(hb_ctx* c) { for (auto& e : g_extra) if (e.first == c) return e.second; return nullptr; }
+
+// folds a finished slot's phase timings into the context totals (slot->done must have completed)
+void fold_timing(hb_ctx* c, JobSlot& s) {
+    if (!s.pending) return;
+    s.pending = false;
+    float a = 0, b = 0;
+    if (cudaEventElapsedTime(&a, s.t[0], s.t[1]) != cudaSuccess || cudaEventElapsedTime(&b, s.t[1], s.t[2]) != cudaSuccess) return;
+    const double pbs = s.first_is_pbs ? a : b, ks = s.first_is_pbs ? b : a;
+    c->stats.pbs_ms = pbs; c->stats.ks_ms = ks;
+    c->stats.pbs_ms_total += pbs; c->stats.ks_ms_total += ks;
+}
 
 hb_status check_ready(hb_ctx* c) {
     if (!c) return HB_ERR_ARG;
@@ -186,6 +201,7 @@ hb_status upload_jobs(hb_ctx* c, const std::vector<PbsJob>& pj, const std::vecto
     CtxExtra* ex = extra_of(c);
     JobSlot& s = ex->slots[ex->next++ % NSLOT];
     CU(c, cudaEventSynchronize(s.done));
+    fold_timing(c, s);
     const size_t a = pj.size() * sizeof(PbsJob), b = kj.size() * sizeof(KsJob), d = lj.size() * sizeof(LinJob);
     const size_t oa = 0, ob = (a + 15) & ~(size_t)15, od = ob + ((b + 15) & ~(size_t)15), tot = od + d + 16;
     CU(c, s.pin.ensure(tot));
@@ -260,7 +276,10 @@ hb_status hb_ctx_create(int32_t device, hb_ctx** out) {
     for (auto& ev : c->ev) CU(nullptr, cudaEventCreate(&ev));
     CU(nullptr, cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
     CtxExtra* ex = new CtxExtra();
-    for (auto& s : ex->slots) { CU(nullptr, cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming)); }
+    for (auto& s : ex->slots) {
+        CU(nullptr, cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+        for (auto& t : s.t) CU(nullptr, cudaEventCreate(&t));
+    }
     g_extra.emplace_back(c, ex);
     *out = c;
     return HB_OK;
@@ -274,7 +293,10 @@ hb_status hb_ctx_destroy(hb_ctx* c) {
     c->jobs_pin.release(); c->stage_pin.release();
     for (size_t i = 0; i < g_extra.size(); ++i)
         if (g_extra[i].first == c) {
-            for (auto& s : g_extra[i].second->slots) { s.pin.release(); s.dev.release(); cudaEventDestroy(s.done); }
+            for (auto& s : g_extra[i].second->slots) {
+                s.pin.release(); s.dev.release(); cudaEventDestroy(s.done);
+                for (auto& t : s.t) cudaEventDestroy(t);
+            }
             delete g_extra[i].second; g_extra.erase(g_extra.begin() + i); break;
         }
     for (auto& ev : c->ev) cudaEventDestroy(ev);
@@ -430,6 +452,29 @@ hb_status hb_wires_read(hb_wires* w, const uint32_t* idx, uint32_t cnt, void* ho
     return HB_OK;
 }
 
+hb_status hb_wires_write_rows(hb_wires* w, uint32_t first, uint32_t cnt, const void* host) {
+    if (!w || (!host && cnt)) return HB_ERR_ARG;
+    if (!cnt) return HB_OK;
+    hb_ctx* c = w->ctx;
+    if ((uint64_t)first + cnt > w->n_wires) return fail(c, HB_ERR_ARG, "wire row range out of bounds");
+    CU(c, cudaSetDevice(c->device));
+    const size_t ts = tsize(c), words = ct_words(c), stride = hb_wire_stride(c);
+    CU(c, cudaMemcpy2DAsync((char*)w->dev + (size_t)first * stride * ts, stride * ts, host, words * ts, words * ts, cnt, cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    return HB_OK;
+}
+hb_status hb_wires_read_rows(hb_wires* w, uint32_t first, uint32_t cnt, void* host) {
+    if (!w || (!host && cnt)) return HB_ERR_ARG;
+    if (!cnt) return HB_OK;
+    hb_ctx* c = w->ctx;
+    if ((uint64_t)first + cnt > w->n_wires) return fail(c, HB_ERR_ARG, "wire row range out of bounds");
+    CU(c, cudaSetDevice(c->device));
+    const size_t ts = tsize(c), words = ct_words(c), stride = hb_wire_stride(c);
+    CU(c, cudaMemcpy2DAsync(host, words * ts, (const char*)w->dev + (size_t)first * stride * ts, stride * ts, words * ts, cnt, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    return HB_OK;
+}
+
 hb_status hb_wires_set_trivial(hb_wires* w, const uint32_t* idx, uint32_t cnt, const uint64_t* pt) {
     if (!w || !idx || !pt) return HB_ERR_ARG;
     hb_ctx* c = w->ctx;
@@ -452,12 +497,13 @@ hb_status hb_sync(hb_ctx* c) {
 
 hb_status hb_stats(hb_ctx* c, hb_stats_t* out) {
     if (!c || !out) return HB_ERR_ARG;
-    if (c->stats.levels) {
-        CU(c, cudaEventSynchronize(c->ev[2]));
-        float a = 0, b = 0;
-        CU(c, cudaEventElapsedTime(&a, c->ev[0], c->ev[1]));
-        CU(c, cudaEventElapsedTime(&b, c->ev[1], c->ev[2]));
-        if (c->p.order == 0) { c->stats.pbs_ms = a; c->stats.ks_ms = b; } else { c->stats.ks_ms = a; c->stats.pbs_ms = b; }
+    CtxExtra* ex = extra_of(c);
+    // drain in submission order so pbs_ms / ks_ms end up describing the latest level
+    for (uint64_t q = 0; q < NSLOT; ++q) {
+        JobSlot& s = ex->slots[(ex->next + q) % NSLOT];
+        if (!s.pending) continue;
+        CU(c, cudaEventSynchronize(s.done));
+        fold_timing(c, s);
     }
     *out = c->stats;
     return HB_OK;
@@ -581,21 +627,22 @@ hb_status hb_eval_level(hb_ctx* c, hb_wires* w, const hb_gate* gates, uint32_t n
     if (hb_status s = upload_jobs(c, pj, kj, lj, &dp, &dk, &dl, &slot)) return s;
     const uint32_t wstride = hb_wire_stride(c);
     const size_t ts = tsize(c);
-    CU(c, cudaEventRecord(c->ev[0], c->stream));
+    CU(c, cudaEventRecord(slot->t[0], c->stream));
     if (p.order == 0) {
         const uint32_t bstride = pad4(big_words(c));
         CU(c, c->scratch_a.ensure((size_t)pj.size() * bstride * ts));
         if (hb_status s = launch_pbs(c, w->dev, wstride, c->scratch_a.p, bstride, dp, (uint32_t)pj.size())) return s;
-        CU(c, cudaEventRecord(c->ev[1], c->stream));
+        CU(c, cudaEventRecord(slot->t[1], c->stream));
         if (hb_status s = launch_ks(c, c->scratch_a.p, bstride, w->dev, wstride, dk, (uint32_t)kj.size())) return s;
     } else {
         const uint32_t sstride = pad4(small_words(c));
         CU(c, c->scratch_b.ensure((size_t)kj.size() * sstride * ts));
         if (hb_status s = launch_ks(c, w->dev, wstride, c->scratch_b.p, sstride, dk, (uint32_t)kj.size())) return s;
-        CU(c, cudaEventRecord(c->ev[1], c->stream));
+        CU(c, cudaEventRecord(slot->t[1], c->stream));
         if (hb_status s = launch_pbs(c, c->scratch_b.p, sstride, w->dev, wstride, dp, (uint32_t)pj.size())) return s;
     }
-    CU(c, cudaEventRecord(c->ev[2], c->stream));
+    CU(c, cudaEventRecord(slot->t[2], c->stream));
+    slot->first_is_pbs = p.order == 0; slot->pending = true;
     if (hb_status s = launch_lin(c, w->dev, wstride, dl, (uint32_t)lj.size(), ct_words(c))) return s;
     CU(c, cudaEventRecord(slot->done, c->stream));
     c->stats.levels++;
@@ -623,15 +670,15 @@ hb_status hb_pbs_batch(hb_ctx* c, const void* lwe_in, const void* tv, int32_t sh
     }
     const PbsJob* dp; const KsJob* dk; const LinJob* dl; JobSlot* slot;
     if (hb_status s = upload_jobs(c, pj, {}, {}, &dp, &dk, &dl, &slot)) return s;
-    CU(c, cudaEventRecord(c->ev[0], c->stream));
+    CU(c, cudaEventRecord(slot->t[0], c->stream));
     if (hb_status s = launch_pbs(c, c->scratch_a.p, sw, c->scratch_b.p, bw, dp, count)) return s;
-    CU(c, cudaEventRecord(c->ev[1], c->stream));
-    CU(c, cudaEventRecord(c->ev[2], c->stream));
+    CU(c, cudaEventRecord(slot->t[1], c->stream));
+    CU(c, cudaEventRecord(slot->t[2], c->stream));
+    slot->first_is_pbs = 1; slot->pending = true;
     CU(c, cudaEventRecord(slot->done, c->stream));
     CU(c, cudaMemcpyAsync(lwe_out, c->scratch_b.p, out_b, cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
     c->stats.levels++;
-    if (c->p.order == 1) { /* ev[0..1] bracket the PBS here regardless of order */ }
     return HB_OK;
 }
 

@@ -29,7 +29,8 @@ class HbGate(C.Structure):
 
 class HbStats(C.Structure):
     _fields_ = [("pbs_count", C.c_uint64), ("ks_count", C.c_uint64), ("levels", C.c_uint64),
-                ("pbs_ms", C.c_double), ("ks_ms", C.c_double), ("kernel_launches", C.c_uint64)]
+                ("pbs_ms", C.c_double), ("ks_ms", C.c_double), ("kernel_launches", C.c_uint64),
+                ("pbs_ms_total", C.c_double), ("ks_ms_total", C.c_double)]
 
 
 GATE_DTYPE = np.dtype([("op", np.uint8), ("arity", np.uint8), ("flags", np.uint16), ("in", np.uint32, (4,)),
@@ -38,7 +39,7 @@ assert GATE_DTYPE.itemsize == C.sizeof(HbGate) == 32
 
 EXPORTS = ["hb_ctx_create", "hb_ctx_destroy", "hb_last_error", "hb_set_params", "hb_load_bsk", "hb_load_ksk",
            "hb_wires_create", "hb_wires_attach", "hb_wires_destroy", "hb_ct_words", "hb_wire_stride",
-           "hb_wires_device_ptr", "hb_wires_write", "hb_wires_read", "hb_wires_set_trivial", "hb_eval_level",
+           "hb_wires_device_ptr", "hb_wires_write", "hb_wires_read", "hb_wires_write_rows", "hb_wires_read_rows", "hb_wires_set_trivial", "hb_eval_level",
            "hb_sync", "hb_stats", "hb_stream", "hb_pbs_batch", "hb_keyswitch_batch", "hb_measure_fp64_peak"]
 
 _LIB = None
@@ -74,6 +75,8 @@ def lib():
         L.hb_wires_device_ptr.argtypes = [vp]
         L.hb_wires_write.argtypes = [vp, vp, u32, vp]
         L.hb_wires_read.argtypes = [vp, vp, u32, vp]
+        L.hb_wires_write_rows.argtypes = [vp, u32, u32, vp]
+        L.hb_wires_read_rows.argtypes = [vp, u32, u32, vp]
         L.hb_wires_set_trivial.argtypes = [vp, vp, u32, vp]
         L.hb_eval_level.argtypes = [vp, vp, vp, u32]
         L.hb_sync.argtypes = [vp]
@@ -225,6 +228,16 @@ class Wires:
         if out is None:
             out = np.zeros((count, self.eng.ct_words), dtype=self.eng.dtype)
         self.eng._ck(self.eng.L.hb_wires_read(self.h, _ptr(idx), count, _ptr(out)), "hb_wires_read")
+        return out
+
+    def write_rows(self, first, cts):
+        """cts: C-contiguous [cnt, ct_words] host array (pinned for full PCIe speed) -> rows [first, first+cnt)."""
+        assert cts.dtype == self.eng.dtype and cts.flags.c_contiguous and cts.shape[1] == self.eng.ct_words
+        self.eng._ck(self.eng.L.hb_wires_write_rows(self.h, first, cts.shape[0], _ptr(cts)), "hb_wires_write_rows")
+
+    def read_rows(self, first, out):
+        assert out.dtype == self.eng.dtype and out.flags.c_contiguous and out.shape[1] == self.eng.ct_words
+        self.eng._ck(self.eng.L.hb_wires_read_rows(self.h, first, out.shape[0], _ptr(out)), "hb_wires_read_rows")
         return out
 
     def set_trivial(self, idx, plaintexts):

@@ -63,6 +63,7 @@ typedef struct {
     uint64_t pbs_count, ks_count, levels;
     double pbs_ms, ks_ms;               /* device time of the last hb_eval_level / batch call */
     uint64_t kernel_launches;           /* engine kernels launched since context creation */
+    double pbs_ms_total, ks_ms_total;   /* device time summed over every hb_eval_level since creation */
 } hb_stats_t;
 
 hb_status hb_ctx_create(int32_t device, hb_ctx** out);
@@ -85,6 +86,9 @@ void* hb_wires_device_ptr(hb_wires*);
 /* host <-> device: packed rows of hb_ct_words() torus words */
 hb_status hb_wires_write(hb_wires*, const uint32_t* idx, uint32_t cnt, const void* lwe_host);
 hb_status hb_wires_read(hb_wires*, const uint32_t* idx, uint32_t cnt, void* lwe_host);
+/* contiguous rows [first, first+cnt): one strided copy straight from/to the caller's (ideally pinned) buffer */
+hb_status hb_wires_write_rows(hb_wires*, uint32_t first, uint32_t cnt, const void* lwe_host);
+hb_status hb_wires_read_rows(hb_wires*, uint32_t first, uint32_t cnt, void* lwe_host);
 hb_status hb_wires_set_trivial(hb_wires*, const uint32_t* idx, uint32_t cnt, const uint64_t* plaintext);
 
 /* evaluate every gate of one level as one batched launch sequence (asynchronous on the ctx stream).

@@ -79,6 +79,8 @@ def lib():
         L.orc_trivial.argtypes = [vp, C.c_int, u64, vp]
         L.orc_phase.restype = u64
         L.orc_phase.argtypes = [vp, C.c_int, vp]
+        L.orc_encrypt_batch.argtypes = [vp, C.c_int, vp, u64, C.c_uint32, vp]
+        L.orc_phase_batch.argtypes = [vp, C.c_int, vp, C.c_uint32, vp]
         L.orc_decompose.argtypes = [C.c_int, C.c_int, C.c_int, u64, C.POINTER(C.c_int64)]
         L.orc_keyswitch.argtypes = [vp, vp, vp]
         L.orc_pbs.argtypes = [vp, vp, vp, vp, C.c_int]
@@ -153,6 +155,25 @@ class Keys:
     def phase(self, ct, big=0):
         ct = np.ascontiguousarray(ct, dtype=self.dtype)
         return int(self.L.orc_phase(self.h, big, _p(ct)))
+
+    def encrypt_batch(self, pts, seed0, big=0):
+        pts = np.ascontiguousarray(pts, dtype=np.uint64)
+        out = np.zeros((len(pts), self.dim(big) + 1), dtype=self.dtype)
+        self.L.orc_encrypt_batch(self.h, big, _p(pts), seed0, len(pts), _p(out))
+        return out
+
+    def phase_batch(self, cts, big=0):
+        cts = np.ascontiguousarray(cts, dtype=self.dtype).reshape(-1, self.dim(big) + 1)
+        out = np.zeros(cts.shape[0], dtype=np.uint64)
+        self.L.orc_phase_batch(self.h, big, _p(cts), cts.shape[0], _p(out))
+        return out
+
+    def enc_bool_batch(self, bits, seed0):
+        e = 1 << (self.bits - 3)
+        return self.encrypt_batch(np.where(np.asarray(bits).astype(bool), e, 7 * e), seed0, big=0)
+
+    def dec_bool_batch(self, cts, big=0):
+        return self.phase_batch(cts, big) < (1 << (self.bits - 1))
 
     # ---- boolean encoding (reference src/circuit.rs:27-33, :948)
     def enc_bool(self, v, seed):

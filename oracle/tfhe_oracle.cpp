@@ -473,6 +473,17 @@ uint64_t orc_phase(const orc_keys* K, int big, const void* ct) {
     return ph;
 }
 
+void orc_encrypt_batch(const orc_keys* K, int big, const uint64_t* pts, uint64_t seed0, uint32_t count, void* out) {
+    const size_t words = (size_t)(big ? K->p.k * K->p.N : K->p.n) + 1, ts = K->p.torus_bits / 8;
+#pragma omp parallel for schedule(static)
+    for (long i = 0; i < (long)count; ++i) orc_encrypt(K, big, pts[i], seed0 + (uint64_t)i, (char*)out + (size_t)i * words * ts);
+}
+void orc_phase_batch(const orc_keys* K, int big, const void* cts, uint32_t count, uint64_t* out) {
+    const size_t words = (size_t)(big ? K->p.k * K->p.N : K->p.n) + 1, ts = K->p.torus_bits / 8;
+#pragma omp parallel for schedule(static)
+    for (long i = 0; i < (long)count; ++i) out[i] = orc_phase(K, big, (const char*)cts + (size_t)i * words * ts);
+}
+
 void orc_decompose(int torus_bits, int base_log, int level, uint64_t x, int64_t* out) {
     if (torus_bits == 32) { int32_t d[64]; decompose<uint32_t>((uint32_t)x, base_log, level, d); for (int i = 0; i < level; ++i) out[i] = d[i]; }
     else { int64_t d[64]; decompose<uint64_t>(x, base_log, level, d); for (int i = 0; i < level; ++i) out[i] = d[i]; }

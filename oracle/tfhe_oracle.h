@@ -69,6 +69,10 @@ void orc_encrypt(const orc_keys*, int big, uint64_t plaintext, uint64_t seed, vo
 void orc_trivial(const orc_keys*, int big, uint64_t plaintext, void* ct_out);
 uint64_t orc_phase(const orc_keys*, int big, const void* ct);   /* b - <a,s> */
 
+/* batched client side: ciphertext i uses seed0 + i (identical to orc_encrypt with that seed) */
+void orc_encrypt_batch(const orc_keys*, int big, const uint64_t* plaintexts, uint64_t seed0, uint32_t count, void* cts_out);
+void orc_phase_batch(const orc_keys*, int big, const void* cts, uint32_t count, uint64_t* phases_out);
+
 /* primitives */
 void orc_decompose(int torus_bits, int base_log, int level, uint64_t x, int64_t* digits_out /* [level], index l-1 = level l */);
 void orc_keyswitch(const orc_keys*, const void* ct_big, void* ct_small);
