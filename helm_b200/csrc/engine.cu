@@ -139,7 +139,7 @@ struct Inst {
         return cudaGetLastError();
     }
     static cudaError_t bsk_fft(const void* std_bsk, double2* out, const double2* wtab, size_t polys, cudaStream_t s) {
-        const double scale = (sizeof(T) == 4 ? 1.0 : 1.0 / 4294967296.0) / (double)(N / 2);
+        const double scale = (sizeof(T) == 4 ? 1.0 : 1.0 / 18446744073709551616.0) / (double)(N / 2);
         bsk_fft_kernel<T, N, RA, RB><<<(unsigned)polys, RA > RB ? RA : RB, 0, s>>>((const T*)std_bsk, out, wtab, scale);
         return cudaGetLastError();
     }

@@ -51,16 +51,11 @@ template <> struct TorusOps<uint32_t> {
 };
 template <> struct TorusOps<uint64_t> {
     static constexpr int BITS = 64;
-    __device__ static __forceinline__ uint64_t round_add(double z) {   // z in units of 2^32 LSB
-        const double magic = 6755399441055744.0;
-        const double t = z + magic;
-        const uint32_t ihi = (uint32_t)__double2loint(t);
-        const double r = t - magic;
-        const double lo = fma(z - r, 4294967296.0, magic);
-        const int32_t ilo = __double2loint(lo);
-        int64_t l64 = (int64_t)ilo;
-        if (z - r > 0.0 && ilo < 0) l64 += 4294967296ll;   // frac == +0.5 exactly: +2^31 wrapped
-        return ((uint64_t)ihi << 32) + (uint64_t)l64;
+    // z in torus units (the Fourier BSK carries the 2^-64 scale); |z| reaches ~2^27 before reduction, so reduce
+    // mod 1 in floating point first (exact), then scale to 64-bit fixed point -- tfhe-rs's from_torus (App. A.4)
+    __device__ static __forceinline__ uint64_t round_add(double z) {
+        const double f = z - rint(z);
+        return (uint64_t)__double2ll_rn(f * 18446744073709551616.0);
     }
 };
 

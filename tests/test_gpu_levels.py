@@ -1,0 +1,105 @@
+"""GPU parity of hb_eval_level (the batched replacement of the reference's per-level rayon loop,
+src/circuit.rs:524-543 -> Gate::evaluate_encrypted src/gates.rs:241-280) against the CPU oracle."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _plain(E, op, x, y, s):
+    return {E.AND: x & y, E.NAND: 1 - (x & y), E.OR: x | y, E.NOR: 1 - (x | y), E.XOR: x ^ y,
+            E.XNOR: 1 - (x ^ y), E.MUX: x if s else y, E.NOT: 1 - x, E.COPY: x}[op]
+
+
+@pytest.mark.parametrize("name,reps", [("toy32", 5), ("boolean_default", 1)])
+def test_level_all_gate_types_bit_exact(name, reps, keys_factory, engine_factory, oracle_mod):
+    """Truth tables of tests/gates_test.rs:9-108 as one batched level; ciphertexts bit-identical to the
+    oracle's exact-integer back-end (u32 torus), decryptions equal to the plaintext gate."""
+    from helm_b200 import engine as E
+    K, eng = keys_factory(name), engine_factory(name)
+    ops = [E.AND, E.NAND, E.OR, E.NOR, E.XOR, E.XNOR, E.MUX, E.NOT, E.COPY] * reps
+    ng = len(ops)
+    rng = np.random.default_rng(11)
+    bits = rng.integers(0, 2, size=(ng, 3))
+    n_in = 3 * ng
+    w = eng.wires(n_in + ng)
+    cts = K.enc_bool_batch(bits.reshape(-1), 5000)
+    w.write(np.arange(n_in, dtype=np.uint32), cts)
+    ar = np.arange(ng)
+    gates = E.make_gates(ops, 3 * ar, 3 * ar + 1, n_in + ar, in2=3 * ar + 2)
+    eng.eval_level(w, gates)
+    eng.sync()
+    got = w.read(n_in + ar.astype(np.uint32))
+    for g, op in enumerate(ops):
+        want = K.bool_gate(op, cts[3 * g], cts[3 * g + 1], cts[3 * g + 2], mode=oracle_mod.EXACT)
+        assert np.array_equal(got[g], want), "gate %d op %d differs" % (g, op)
+        x, y, s = (int(v) for v in bits[g])
+        assert K.dec_bool(got[g]) == bool(_plain(E, op, x, y, s))
+    w.close()
+
+
+def test_two_levels_chain_and_row_io(keys_factory, engine_factory):
+    """level 2 consumes level 1's outputs straight from the device-resident wire array; row-range IO."""
+    from helm_b200 import engine as E
+    K, eng = keys_factory("toy32"), engine_factory("toy32")
+    W = 70                                   # ragged vs the 2-gate PBS tile and the 16-gate KS tile
+    rng = np.random.default_rng(3)
+    b0 = rng.integers(0, 2, size=W)
+    w = eng.wires(3 * W)
+    w.write_rows(0, K.enc_bool_batch(b0, 900))
+    cur = b0
+    for lvl in (1, 2):
+        ops = rng.integers(0, 6, size=W).astype(np.uint8)
+        i0 = rng.integers(0, W, size=W); i1 = rng.integers(0, W, size=W)
+        eng.eval_level(w, E.make_gates(ops, (lvl - 1) * W + i0, (lvl - 1) * W + i1, lvl * W + np.arange(W)))
+        cur = np.array([_plain(E, int(o), int(cur[a]), int(cur[b]), 0) for o, a, b in zip(ops, i0, i1)])
+    eng.sync()
+    out = np.zeros((W, eng.ct_words), dtype=eng.dtype)
+    w.read_rows(2 * W, out)
+    assert np.array_equal(K.dec_bool_batch(out), cur.astype(bool))
+    w.close()
+
+
+def test_empty_level_and_errors(keys_factory, engine_factory):
+    import helm_b200
+    from helm_b200 import engine as E
+    eng = engine_factory("toy32")
+    w = eng.wires(8)
+    eng.eval_level(w, E.make_gates([], [], [], []))          # empty level is a no-op
+    with pytest.raises(helm_b200.EngineError, match="out of range"):
+        eng.eval_level(w, E.make_gates([E.AND], [0], [1], [99]))
+    with pytest.raises(helm_b200.EngineError):
+        eng.eval_level(w, E.make_gates([E.LUT], [0], [1], [2]))   # LUT needs shortint (order 1) parameters
+    w.close()
+
+
+@pytest.mark.parametrize("name", ["toy64", "toy64b"])
+def test_shortint_lut_level(name, keys_factory, engine_factory, oracle_mod):
+    """LUT mode (src/gates.rs:754-785, 2-input path): KS -> PBS with the boxed accumulator.  u64 torus through
+    the f64 FFT is not bit-exact, so: decryptions equal the table, and the phase differs from the oracle's
+    exact-integer result by far less than the encoding step."""
+    from helm_b200 import engine as E
+    K, eng = keys_factory(name), engine_factory(name)
+    tables = [0x8, 0x6, 0xE, 0x1, 0x9, 0x7]
+    ng = 4 * len(tables)
+    w = eng.wires(2 * ng + ng)
+    bits = np.array([[(g >> 1) & 1, g & 1] for g in range(ng)])
+    cts = np.stack([K.enc_shortint(int(b), 700 + i) for i, b in enumerate(bits.reshape(-1))])
+    w.write(np.arange(2 * ng, dtype=np.uint32), cts)
+    ar = np.arange(ng)
+    luts = np.array([tables[g // 4] for g in range(ng)], dtype=np.uint64)
+    eng.eval_level(w, E.make_gates([E.LUT] * ng, 2 * ar, 2 * ar + 1, 2 * ng + ar, lut=luts, arity=[2] * ng))
+    eng.sync()
+    got = w.read((2 * ng + ar).astype(np.uint32))
+    mc = K.P.msg_mod * K.P.carry_mod
+    for g in range(ng):
+        a, b = (int(v) for v in bits[g])
+        want_bit = (int(luts[g]) >> (a * 2 + b)) & 1
+        assert K.dec_shortint(got[g]) == want_bit, "gate %d" % g
+        lin = (cts[2 * g] * K.dtype(2) + cts[2 * g + 1]).astype(K.dtype)
+        table = [(int(luts[g]) >> x) & 1 if x < 4 else 0 for x in range(mc)]
+        ref = K.shortint_lut(lin, table, mode=oracle_mod.EXACT)
+        d = (K.phase(got[g], 1) - K.phase(ref, 1)) % (1 << 64)
+        d = min(d, (1 << 64) - d)
+        assert d < K.delta() >> 12, "phase differs from the exact oracle by 2^%.1f" % np.log2(max(d, 1))
+    w.close()

@@ -47,3 +47,24 @@ def test_pbs_arbitrary_test_vector(keys_factory, engine_factory, oracle_mod):
         tv[K.k] = tvb[i]
         want = K.pbs(cts[i], tv.reshape(-1), mode=oracle_mod.EXACT)
         assert np.array_equal(got[i], want)
+
+
+@pytest.mark.parametrize("name", ["toy64", "toy64b"])
+def test_pbs_u64_close_to_exact(name, keys_factory, engine_factory, oracle_mod):
+    """u64 torus: the f64 FFT cannot be bit-exact (53-bit mantissa), exactly as in tfhe-rs.  The output phase must
+    agree with the exact-integer oracle to well below the scheme noise, and with the oracle's own f64-FFT
+    back-end to the same order."""
+    K, eng = keys_factory(name), engine_factory(name)
+    rng = np.random.default_rng(9)
+    cnt = 3
+    cts = rng.integers(0, 2 ** 63, size=(cnt, K.n + 1), dtype=np.uint64) * np.uint64(2)
+    mc = K.P.msg_mod * K.P.carry_mod
+    tv = K.shortint_accumulator(list(range(mc))).reshape(K.k + 1, K.N)
+    got = eng.pbs_batch(cts, tv[K.k][None, :])
+    for i in range(cnt):
+        want = K.pbs(cts[i], tv.reshape(-1), mode=oracle_mod.EXACT)
+        d = (got[i].astype(np.int64) - want.astype(np.int64))          # wrapping difference per word
+        worst = int(np.abs(d).max())
+        assert worst < 1 << 40, "word error 2^%.1f (torus 2^%.1f)" % (np.log2(max(worst, 1)), np.log2(max(worst, 1)) - 64)
+        ph = (K.phase(got[i], 1) - K.phase(want, 1)) % (1 << 64)
+        assert min(ph, (1 << 64) - ph) < K.delta() >> 12
