@@ -50,21 +50,25 @@ def test_pbs_arbitrary_test_vector(keys_factory, engine_factory, oracle_mod):
 
 
 @pytest.mark.parametrize("name", ["toy64", "toy64b"])
-def test_pbs_u64_close_to_exact(name, keys_factory, engine_factory, oracle_mod):
-    """u64 torus: the f64 FFT cannot be bit-exact (53-bit mantissa), exactly as in tfhe-rs.  The output phase must
-    agree with the exact-integer oracle to well below the scheme noise, and with the oracle's own f64-FFT
-    back-end to the same order."""
+def test_pbs_u64_phase_parity(name, keys_factory, engine_factory, oracle_mod):
+    """u64 torus: the f64 FFT cannot be bit-exact (53-bit mantissa), exactly as in tfhe-rs, and a single flipped
+    rounding in one decomposition digit changes every later ciphertext word -- so words are not comparable, phases
+    are.  (1) With <= 1 non-zero mask element there is no feedback: words agree with the exact-integer oracle to
+    the f64 rounding level.  (2) On real encryptions the decrypted phase equals the looked-up value and sits within
+    the scheme's noise of the exact oracle's phase."""
     K, eng = keys_factory(name), engine_factory(name)
-    rng = np.random.default_rng(9)
-    cnt = 3
-    cts = rng.integers(0, 2 ** 63, size=(cnt, K.n + 1), dtype=np.uint64) * np.uint64(2)
     mc = K.P.msg_mod * K.P.carry_mod
     tv = K.shortint_accumulator(list(range(mc))).reshape(K.k + 1, K.N)
-    got = eng.pbs_batch(cts, tv[K.k][None, :])
-    for i in range(cnt):
-        want = K.pbs(cts[i], tv.reshape(-1), mode=oracle_mod.EXACT)
-        d = (got[i].astype(np.int64) - want.astype(np.int64))          # wrapping difference per word
-        worst = int(np.abs(d).max())
-        assert worst < 1 << 40, "word error 2^%.1f (torus 2^%.1f)" % (np.log2(max(worst, 1)), np.log2(max(worst, 1)) - 64)
-        ph = (K.phase(got[i], 1) - K.phase(want, 1)) % (1 << 64)
-        assert min(ph, (1 << 64) - ph) < K.delta() >> 12
+    ct = np.zeros(K.n + 1, dtype=np.uint64)
+    ct[3] = np.uint64(0x4000000000000000); ct[K.n] = np.uint64(12345 << 50)
+    got = eng.pbs_batch(ct[None, :], tv[K.k][None, :])[0]
+    want = K.pbs(ct, tv.reshape(-1), mode=oracle_mod.EXACT)
+    assert int(np.abs((got - want).astype(np.int64)).max()) < 1 << 44
+    small = np.stack([K.encrypt(m * K.delta(), 300 + m, big=0) for m in range(mc // 2)])
+    got = eng.pbs_batch(small, tv[K.k][None, :])
+    for m in range(mc // 2):
+        want = K.pbs(small[m], tv.reshape(-1), mode=oracle_mod.EXACT)
+        d = (K.phase(got[m], 1) - K.phase(want, 1)) % (1 << 64)
+        assert min(d, (1 << 64) - d) < K.delta() >> 6
+        ideal = (K.phase(got[m], 1) - m * K.delta()) % (1 << 64)
+        assert min(ideal, (1 << 64) - ideal) < K.delta() >> 4
