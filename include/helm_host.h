@@ -1,0 +1,56 @@
+/*
+ * helm_host.h -- C ABI of the host-side mirror of HELM's circuit surface (libhelm_host.so), used by tests, by the
+ * `helm` CLI and by bindings.  It wraps helm_b200/csrc/host/: read_verilog_file (reference src/verilog_parser.rs:138),
+ * Circuit::{sort_circuit, compute_levels, evaluate} (src/circuit.rs:122-381) and the EvalCircuit implementations
+ * GateCircuit / LutCircuit (src/circuit.rs:449-577, 969-1111), which run every level as one hb_eval_level batch.
+ * Text results are written into caller buffers as "name=value\n" lines.  All functions return 0 on success;
+ * hh_last_error() describes the last failure on this thread (reference panics become errors).
+ */
+#ifndef HELM_HOST_H
+#define HELM_HOST_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct hh_circuit hh_circuit;
+typedef struct hh_session hh_session;
+
+const char* hh_last_error(void);
+
+/* netlist + levelization (no GPU needed) */
+int hh_circuit_load(const char* verilog_path, int is_arith, int strict_reference_levels, hh_circuit** out);
+int hh_circuit_load_text(const char* verilog_text, int is_arith, int strict_reference_levels, hh_circuit** out);
+void hh_circuit_free(hh_circuit*);
+/* what: 0 gates, 1 wire_set, 2 inputs (with duplicates, DFF outputs appended), 3 outputs, 4 dff_outputs, 5 levels
+ * (DFF level included), 6 has_luts, 7 has_arith, 8 bootstrapped gates (PBS gates; MUX counts once) */
+int64_t hh_circuit_count(const hh_circuit*, int what);
+int64_t hh_circuit_level_width(const hh_circuit*, int level_index);
+/* "level:type:name:out:in0,in1,...\n" per gate in level order */
+int hh_circuit_describe(const hh_circuit*, char* buf, size_t cap, size_t* needed);
+/* plaintext evaluation: inputs as "wire=value\n" lines (empty => all false/0); ptxt_type "bool" | "u8".."u128";
+ * cycles > 1 feeds the wire map back like the reference main loop.  Writes every wire with a value. */
+int hh_circuit_eval_plain(const hh_circuit*, const char* inputs, const char* ptxt_type, int cycles,
+                          char* buf, size_t cap, size_t* needed);
+/* CSV helper (reference read_input_wires): file -> "wire=value\n" lines */
+int hh_read_input_csv(const char* path, const char* ptxt_type, char* buf, size_t cap, size_t* needed);
+
+/* encrypted evaluation on the GPU engine.  Keys: generated here from a seed (raw pointers NULL), or supplied by the
+ * caller (tfhe-rs in the drop-in; the oracle in tests): lwe_sk n bytes, glwe_sk kN bytes, bsk/ksk standard domain. */
+int hh_session_create(const char* param_set, int device, uint64_t seed,
+                      const uint8_t* lwe_sk, const uint8_t* glwe_sk, const void* bsk, size_t bsk_bytes,
+                      const void* ksk, size_t ksk_bytes, hh_session** out);
+void hh_session_free(hh_session*);
+/* encrypt_inputs -> cycles x (evaluate_encrypted [+ evaluate_ready]) -> decrypt_outputs.  Output wires as
+ * "wire=value\n"; if all_wires != 0 every wire that carries a value is decrypted (the reference's tests compare every
+ * wire with the plaintext evaluation).  seconds[3] = encrypt, evaluate, decrypt wall times (may be NULL). */
+int hh_session_run(hh_session*, const hh_circuit*, const char* inputs, int cycles, int all_wires, int verbose,
+                   char* buf, size_t cap, size_t* needed, double* seconds);
+/* engine statistics of the session: pbs_count, ks_count, levels, kernel_launches */
+int hh_session_stats(hh_session*, uint64_t* out4);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

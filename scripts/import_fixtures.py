@@ -1,0 +1,23 @@
+#!/usr/bin/env python
+"""Copies the benchmark DATA files the reference's own tests and BASELINE.json configs use (structural-Verilog
+netlists and input/golden CSVs from the hdl-benchmarks submodule -- circuit descriptions, not reference code) into
+tests/golden/netlists and tests/golden/test-cases, because /root/reference does not exist on the GPU box.
+Run here (CPU container) only.  Provenance: TrustworthyComputing/hdl-benchmarks @ d949d36."""
+import os, shutil, sys
+SRC = "/root/reference/hdl-benchmarks"
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+NETS = ["processed-netlists/" + f for f in ("s27.v", "2-bit-adder.v", "c17.v", "16-bit-mult-gates.v", "8-bit-adder-lut-2-1.v",
+        "8-bit-adder-lut-3-1.v", "chi_squared_arith.v", "invalid.v", "gates.v", "c17_lut_2.v")] + \
+       ["netlists/c880.v", "netlists/c7552.v"]
+CASES = ["2-bit-adder.inputs.csv", "2-bit-adder.outputs.csv", "8-bit-adder.inputs.csv", "bool_array.input.csv",
+         "16-bit-mult.inputs.csv"] + ["chi_squared_arith_%d.%s.csv" % (i, k) for i in range(1, 5) for k in ("inputs", "outputs")]
+for rel in NETS:
+    sub = "yosys" if rel.startswith("netlists/") else "netlists"
+    dst = os.path.join(ROOT, "tests", "golden", sub)
+    os.makedirs(dst, exist_ok=True)
+    shutil.copy(os.path.join(SRC, rel), dst)
+dst = os.path.join(ROOT, "tests", "golden", "test-cases")
+os.makedirs(dst, exist_ok=True)
+for f in CASES:
+    shutil.copy(os.path.join(SRC, "test-cases", f), dst)
+print("imported", len(NETS), "netlists and", len(CASES), "csv files")

@@ -1,0 +1,134 @@
+"""Host-side logic without a GPU: the reference's parser / circuit tests restated against the C++ host library
+(tests/verilog_parser_test.rs:4-141, tests/circuit_test.rs:17-45) plus the netlist statistics of SURVEY.md App. B."""
+import os
+
+import pytest
+
+from helm_b200 import host as H
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+NET = os.path.join(G, "netlists")
+CASES = os.path.join(G, "test-cases")
+C = H.Circuit
+
+
+def test_header_symbols_exported():
+    import re
+    src = open(os.path.join(os.path.dirname(G), "..", "include", "helm_host.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    syms = sorted(set(re.findall(r"\b(hh_[a-z0-9_]+)\s*\(", src)))
+    L = H.lib()
+    for s in syms:
+        assert hasattr(L, s), s
+    assert sorted(H.EXPORTS) == syms
+
+
+def test_parse_two_bit_adder():                       # verilog_parser_test.rs:4-13
+    c = C(os.path.join(NET, "2-bit-adder.v"))
+    assert c.count(C.GATES) == 10 and c.count(C.WIRES) == 10 and c.count(C.INPUTS) == 5
+    assert c.count(C.HAS_LUTS) == 0 and c.count(C.HAS_ARITH) == 0
+
+
+def test_input_wires_parser():                        # verilog_parser_test.rs:15-27, 60-75
+    w = H.read_input_wires(os.path.join(CASES, "2-bit-adder.inputs.csv"))
+    assert w == {"a[0]": True, "a[1]": False, "b[0]": False, "b[1]": True, "cin": False}
+    c = C(os.path.join(NET, "2-bit-adder.v"))
+    assert set(w) == {g for g in c.evaluate(w) if "[" in g and g[0] in "ab"} | {"cin"}
+
+
+def test_arithmetic_parser_and_int_types():           # verilog_parser_test.rs:29-47, 77-118
+    c = C(os.path.join(NET, "chi_squared_arith.v"), is_arith=True)
+    assert c.count(C.HAS_ARITH) == 1 and c.count(C.GATES) == 14 and c.count(C.INPUTS) == 3 and c.count(C.OUTPUTS) == 4
+    for t in ("u8", "u16", "u32", "u64", "u128"):
+        assert H.read_input_wires(os.path.join(CASES, "chi_squared_arith_1.inputs.csv"), t) == {"N0": 2, "N1": 7, "N2": 9}
+
+
+def test_invalid_netlist_mixes_luts_and_arith():      # verilog_parser_test.rs:49-58 (#[should_panic])
+    with pytest.raises(H.HostError, match="mix LUTs with arithmetic"):
+        C(os.path.join(NET, "invalid.v"), is_arith=True)
+
+
+def test_bool_array_csv_hex_expansion():              # verilog_parser_test.rs:120-141
+    w = H.read_input_wires(os.path.join(CASES, "bool_array.input.csv"))
+    assert [w["in1[%d]" % i] for i in range(4)] == [True, False, True, True]
+    assert [w["in2[%d]" % i] for i in range(4)] == [False, True, False, True]              # 0xA LSB first
+    assert [w["in3[%d]" % i] for i in range(6)] == [True, True, False, True, False, False]  # 0xB zero padded
+    assert len(w) == 14
+
+
+def test_two_bit_adder_plaintext():                   # circuit_test.rs:17-45
+    c = C(os.path.join(NET, "2-bit-adder.v"))
+    v = c.evaluate({k: True for k in ("a[0]", "a[1]", "b[0]", "b[1]", "cin")})
+    assert len(v) == 15
+    assert v["sum[0]"] and v["sum[1]"] and v["cout"] and not v["i0"] and not v["i1"]
+    assert [g[2] for g in c.gates() if g[0] == 1] == ["a1", "a3", "x1", "x3"]      # level order is by name
+
+
+@pytest.mark.parametrize("name,levels,widths,pbs", [
+    ("s27.v", 6, [4, 3, 1, 1, 2, 3], 7),
+    ("c17.v", 4, None, 6),
+    ("16-bit-mult-gates.v", 31, None, 684),
+    ("8-bit-adder-lut-3-1.v", 8, None, 15),
+    ("8-bit-adder-lut-2-1.v", 14, None, 34),
+])
+def test_levelization_statistics(name, levels, widths, pbs):
+    c = C(os.path.join(NET, name))
+    assert c.count(C.LEVELS) == levels and c.count(C.PBS_GATES) == pbs
+    if widths:
+        assert c.level_widths() == widths
+
+
+def test_s27_all_false_and_sequential():              # BASELINE config 1: no inputs => all false, G17 = true
+    c = C(os.path.join(NET, "s27.v"))
+    assert c.evaluate()["G17"] is True
+    v3 = c.evaluate(cycles=3)
+    assert isinstance(v3["G17"], bool) and c.count(C.DFFS) == 3
+
+
+def test_lut_adders_compute_54():                     # 19 + 35 (8-bit-adder.inputs.csv); the stale outputs csv says 4
+    ins = H.read_input_wires(os.path.join(CASES, "8-bit-adder.inputs.csv"))
+    for name in ("8-bit-adder-lut-2-1.v", "8-bit-adder-lut-3-1.v"):
+        c = C(os.path.join(NET, name))
+        full = dict(ins)
+        full.update({"G11": False, "G12": False} if False else {})
+        v = c.evaluate(_with_bus_names(c, ins))
+        assert sum(int(v["G14[%d]" % i]) << i for i in range(8)) == 54, name
+
+
+def _with_bus_names(c, ins):
+    """8-bit-adder-lut-2-1.v declares the bus and its bits: every declared input needs a value."""
+    need = {}
+    try:
+        c.evaluate(ins)
+        return ins
+    except H.HostError as e:
+        import re
+        m = re.search(r'Input wire "([^"]+)"', str(e))
+        while m:
+            need[m.group(1)] = False
+            try:
+                c.evaluate({**ins, **need})
+                break
+            except H.HostError as e2:
+                m = re.search(r'Input wire "([^"]+)"', str(e2))
+    return {**ins, **need}
+
+
+@pytest.mark.parametrize("i", [1, 2, 3, 4])
+def test_chi_squared_goldens_plain(i):                # circuit_test.rs:314-474 golden CSVs (valid at u16 and u32)
+    c = C(os.path.join(NET, "chi_squared_arith.v"), is_arith=True)
+    for t in ("u16", "u32"):
+        ins = H.read_input_wires(os.path.join(CASES, "chi_squared_arith_%d.inputs.csv" % i), t)
+        want = H.read_input_wires(os.path.join(CASES, "chi_squared_arith_%d.outputs.csv" % i), t)
+        got = c.evaluate(ins, t)
+        assert {k: got[k] for k in want} == want
+
+
+def test_numeric_wire_names_quirk():
+    txt = "module m(a, b, y);\n input a, b;\n output y;\n and g2(a, b, 10);\n not g1(10, y);\nendmodule\n"
+    ok = C(text=txt)
+    assert ok.level_widths() == [1, 1] and ok.evaluate({"a": True, "b": True})["y"] is False
+    quirk = C(text=txt, strict_reference_levels=True)      # consumer sorts first by name: the reference puts both gates in level 1 (a race)
+    assert quirk.level_widths() == [2]
+    with pytest.raises(H.HostError, match="never become ready"):
+        C(text="module m(a, y);\n input a;\n output y;\n and g1(a, zz, y);\nendmodule\n")
