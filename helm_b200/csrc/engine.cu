@@ -313,6 +313,7 @@ hb_status hb_set_params(hb_ctx* c, const hb_params* p) {
     if (p->n + 1 > KS_NT * KS_QC) return fail(c, HB_ERR_UNSUPPORTED, "n+1 exceeds keyswitch tile (768)");
     if (p->ks_level > KS_MAXL || p->ks_base_log > 7) return fail(c, HB_ERR_UNSUPPORTED, "keyswitch decomposition too wide (level<=8, base_log<=7)");
     if (p->pbs_base_log * p->pbs_level > p->torus_bits || p->pbs_base_log > 31) return fail(c, HB_ERR_ARG, "bad PBS decomposition");
+    if (p->torus_bits == 32 && p->pbs_base_log > 7) return fail(c, HB_ERR_UNSUPPORTED, "u32 torus: pbs_base_log must be <= 7 (digits are staged as bytes)");
     if (p->order == 1 && (p->msg_mod * p->carry_mod < 2 || p->msg_mod * p->carry_mod > 16)) return fail(c, HB_ERR_ARG, "msg_mod*carry_mod must be in [2,16]");
     CU(c, cudaSetDevice(c->device));
     c->p = *p; c->shape = sh; c->have_params = true; c->have_bsk = c->have_ksk = false;

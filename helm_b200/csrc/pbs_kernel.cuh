@@ -89,6 +89,49 @@ template <class T, int L> __device__ __forceinline__ int32_t digit_of(T x, int b
     return dig;
 }
 
+// all L signed digits of x at once (dig[lev] = digit of level lev+1); same recurrence as digit_of
+template <class T, int L> __device__ __forceinline__ void digits_all(T x, int base_log, int32_t (&dig)[L]) {
+    constexpr int BITS = TorusOps<T>::BITS;
+    const int tot = base_log * L;
+    T state = x;
+    if (tot < BITS) {
+        state = x >> (BITS - tot - 1);
+        state = (state + 1) >> 1;
+        state &= (((T)1) << tot) - 1;
+    }
+    const T mask = (((T)1) << base_log) - 1;
+#pragma unroll
+    for (int l = L - 1; l >= 0; --l) {
+        T res = state & mask;
+        state >>= base_log;
+        T carry = ((res - 1) | state) & res;
+        carry >>= (base_log - 1);
+        state += carry;
+        dig[l] = (int32_t)res - (int32_t)(carry << base_log);
+    }
+}
+
+// Digit staging in shared memory between the decomposition pass and the forward-FFT pass.  One pack = the digits of
+// coefficients (c, c+M) for two consecutive j1 (four values): biased bytes when base_log <= 7 (boolean), int32 otherwise.
+template <bool SMALL> struct DigPack;
+template <> struct DigPack<true> {
+    using type = uint32_t;
+    static constexpr int BIAS = 64;
+    __device__ static __forceinline__ type make(int32_t a, int32_t b, int32_t c, int32_t d) {
+        return (uint32_t)(a + BIAS) | ((uint32_t)(b + BIAS) << 8) | ((uint32_t)(c + BIAS) << 16) | ((uint32_t)(d + BIAS) << 24);
+    }
+    template <int K4> __device__ static __forceinline__ double get(type p) {      // exact: 2^52 + byte - (2^52 + 64)
+        return __hiloint2double(0x43300000, (int)__byte_perm(p, 0, 0x4440 | K4)) - 4503599627370560.0;
+    }
+};
+template <> struct DigPack<false> {
+    using type = int4;
+    __device__ static __forceinline__ type make(int32_t a, int32_t b, int32_t c, int32_t d) { return make_int4(a, b, c, d); }
+    template <int K4> __device__ static __forceinline__ double get(type p) {
+        return int2double_exact(K4 == 0 ? p.x : K4 == 1 ? p.y : K4 == 2 ? p.z : p.w);
+    }
+};
+
 template <class T> __device__ __forceinline__ T rot_read(const T* p, int N, int c, int a) {
     int t = c - a; if (t < 0) t += 2 * N;           // a in [0,2N)
     return t < N ? p[t] : (T)(0 - p[t - N]);
@@ -106,6 +149,9 @@ template <class T> __device__ __forceinline__ T tv_body(const PbsJob& jb, int N,
 
 template <class T, int N, int K, int L, int RA, int RB, int G>
 struct PbsCfg {
+    static constexpr bool SMALLDIG = sizeof(T) == 4;      // u32 parameter sets have base_log <= 7 (checked on the host)
+    using Dig = DigPack<SMALLDIG>;
+    static constexpr int PARTS = RA / 2;
     static constexpr int M = N / 2;
     static constexpr int ROWS = (K + 1) * L;
     static constexpr int XROW = RA * (RB + 1);
@@ -114,7 +160,8 @@ struct PbsCfg {
     static_assert(HB_TW_DEN % (4 * RA) == 0 && HB_TW_DEN % RB == 0, "twiddle table too small");
     __host__ __device__ static constexpr size_t smem_bytes(int n) {
         return (size_t)G * ROWS * XROW * sizeof(double2) + 2 * (size_t)M * sizeof(double2) +
-               (size_t)G * (K + 1) * N * sizeof(T) + (((size_t)G * (n + 1) * 2 + 15) & ~(size_t)15);
+               (size_t)G * (K + 1) * N * sizeof(T) + (size_t)G * ROWS * PARTS * RB * sizeof(typename Dig::type) +
+               (((size_t)G * (n + 1) * 2 + 15) & ~(size_t)15);
     }
 };
 
@@ -128,7 +175,11 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
     double2* WA = X + (size_t)G * ROWS * XROW;                          // [RA][RB]  W(j0,k0) at k0*RB+j0
     double2* WB = WA + M;                                               // [RB][RA]  W(j0,k0) at j0*RA+k0
     T* acc = reinterpret_cast<T*>(WB + M);                              // [G][K+1][N]
-    uint16_t* atil = reinterpret_cast<uint16_t*>(acc + (size_t)G * (K + 1) * N);   // [G][n+1]
+    using Dig = typename C::Dig;
+    using DigT = typename Dig::type;
+    constexpr int PARTS = C::PARTS;
+    DigT* digs = reinterpret_cast<DigT*>(acc + (size_t)G * (K + 1) * N);           // [G][ROWS][PARTS][RB]
+    uint16_t* atil = reinterpret_cast<uint16_t*>(digs + (size_t)G * ROWS * PARTS * RB);   // [G][n+1]
 
     const int tid = threadIdx.x;
     const int n = A.n;
@@ -177,24 +228,37 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
         for (int g = 0; g < G; ++g) any |= atil[g * (n + 1) + i];
         if (any == 0) continue;                       // uniform across the CTA
 
-        // P1: rotate-subtract, decompose, twist, radix-RA DFT over j1, inter-stage twiddle
-        for (int t = tid; t < G * ROWS * RB; t += NT) {
-            const int j0 = t % RB, row = (t / RB) % ROWS, g = t / (RB * ROWS);
-            const int lev = row / (K + 1), r = row % (K + 1);
+        // P1a: rotate-subtract and signed decomposition, once per coefficient for all L levels; digits staged in
+        // shared memory in the order the FFT pass reads them ([row][part][j0], part = a pair of j1)
+        for (int t = tid; t < G * (K + 1) * PARTS * RB; t += NT) {
+            const int j0 = t % RB, part = (t / RB) % PARTS, r = (t / (RB * PARTS)) % (K + 1), g = t / (RB * PARTS * (K + 1));
             const int a = atil[g * (n + 1) + i];
             const T* ap = acc + ((size_t)g * (K + 1) + r) * N;
+            int32_t dg[4][L];
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const int c = j0 + RB * (2 * part + u);
+                digits_all<T, L>(rot_read<T>(ap, N, c, a) - ap[c], A.base_log, dg[2 * u]);
+                digits_all<T, L>(rot_read<T>(ap, N, c + M, a) - ap[c + M], A.base_log, dg[2 * u + 1]);
+            }
+#pragma unroll
+            for (int lev = 0; lev < L; ++lev)
+                digs[(((size_t)g * ROWS + lev * (K + 1) + r) * PARTS + part) * RB + j0] = Dig::make(dg[0][lev], dg[1][lev], dg[2][lev], dg[3][lev]);
+        }
+        __syncthreads();
+        // P1b: twist, radix-RA DFT over j1, inter-stage twiddle
+        for (int t = tid; t < G * ROWS * RB; t += NT) {
+            const int j0 = t % RB, grow = t / RB;
+            const DigT* dp = digs + (size_t)grow * PARTS * RB + j0;
             double2 x[RA];
 #pragma unroll
-            for (int j1 = 0; j1 < RA; ++j1) {
-                const int c = j0 + RB * j1;
-                const T d0 = rot_read<T>(ap, N, c, a) - ap[c];
-                const T d1 = rot_read<T>(ap, N, c + M, a) - ap[c + M];
-                const double2 v = make_double2(int2double_exact(digit_of<T, L>(d0, A.base_log, lev)),
-                                               int2double_exact(digit_of<T, L>(d1, A.base_log, lev)));
-                x[j1] = cmul_tw<1>(v, j1 * C::TWA);
+            for (int part = 0; part < PARTS; ++part) {
+                const DigT pk = dp[part * RB];
+                x[2 * part] = cmul_tw<1>(make_double2(Dig::template get<0>(pk), Dig::template get<1>(pk)), (2 * part) * C::TWA);
+                x[2 * part + 1] = cmul_tw<1>(make_double2(Dig::template get<2>(pk), Dig::template get<3>(pk)), (2 * part + 1) * C::TWA);
             }
             dft_regs<RA, 1>(x);
-            double2* xr = X + ((size_t)g * ROWS + row) * XROW;
+            double2* xr = X + (size_t)grow * XROW;
 #pragma unroll
             for (int k0 = 0; k0 < RA; ++k0) xr[k0 * (RB + 1) + j0] = cmul(x[brev<RA>(k0)], WA[k0 * RB + j0]);
         }
