@@ -9,6 +9,7 @@
 #include <vector>
 #include "../../include/helm_b200.h"
 #include "pbs_kernel.cuh"
+#include "pbs16_kernel.cuh"
 #include "ks_kernel.cuh"
 
 using namespace hb;
@@ -146,8 +147,32 @@ struct Inst {
     static constexpr Shape shape() { return Shape{(int)sizeof(T) * 8, N, K, L, RA, RB, G, NT, &smem, &launch, &bsk_fft}; }
 };
 
+// N = 512 shapes run the half-warp-per-polynomial kernel (pbs16_kernel.cuh); the key transform and the Fourier key layout are shared
+template <class T, int K, int L, int G, int MINB>
+struct Inst16 {
+    using C = Pbs16Cfg<T, K, L, G>;
+    static size_t smem(int n) { return C::smem_bytes(n); }
+    static cudaError_t launch(const PbsArgs& a, cudaStream_t s, size_t smem) {
+        auto kern = pbs16_kernel<T, K, L, G, MINB>;
+        static bool attr_done = false;
+        if (!attr_done) {
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+            if (e != cudaSuccess) return e;
+            attr_done = true;
+        }
+        const unsigned grid = (a.n_jobs + G - 1) / G;
+        kern<<<grid, C::NT, smem, s>>>(a);
+        return cudaGetLastError();
+    }
+    static constexpr Shape shape() { return Shape{(int)sizeof(T) * 8, 512, K, L, 16, 16, G, C::NT, &smem, &launch, &Inst<T, 512, K, L, 16, 16, 1, 32, 1>::bsk_fft}; }
+};
+
 const Shape g_shapes[] = {
+#ifdef HB_PBS_V2
     Inst<uint32_t, 512, 2, 3, 16, 16, 2, 288, 2>::shape(),     // tfhe boolean DEFAULT_PARAMETERS
+#else
+    Inst16<uint32_t, 2, 3, 4, 2>::shape(),                     // tfhe boolean DEFAULT_PARAMETERS
+#endif
     Inst<uint32_t, 1024, 1, 3, 16, 32, 1, 192, 2>::shape(),    // concrete-core GPU path of the reference
     Inst<uint64_t, 512, 3, 1, 16, 16, 2, 128, 2>::shape(),     // PARAM_MESSAGE_1_CARRY_1_KS_PBS
     Inst<uint64_t, 2048, 1, 1, 32, 32, 2, 128, 1>::shape(),    // PARAM_MESSAGE_2_CARRY_2_KS_PBS

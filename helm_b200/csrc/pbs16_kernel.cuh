@@ -1,0 +1,257 @@
+// Batched programmable bootstrap for N = 512 (M = 256 = 16 x 16), second-generation mapping (boolean default and
+// PARAM_MESSAGE_1_CARRY_1): same arithmetic as pbs_kernel.cuh (bit-identical results), different work distribution.
+//
+// Why (profiles/r01_v2_*): in pbs_kernel every FFT stage ends in a CTA-wide barrier, the inverse transforms run on a
+// third of the threads and only 4 gates fit one SM; barrier stalls were the top stall reason at 42 % FP64-pipe use.
+//
+// Mapping here: thread = (gate g, polynomial r, idx in [0,16)); the 16 threads of one (g, r) own that accumulator
+// polynomial for the whole blind rotation.  They rotate/decompose it, run its forward FFTs, and later its inverse FFT
+// and the rounding add -- the 16x16 transposes between FFT stages stay inside a half-warp, so those stages are chained
+// with __syncwarp() only.  The single CTA-wide exchange is the pointwise MAC with BSK_i, which mixes polynomials:
+// it is done level by level ((K+1) spectra per gate in shared memory instead of (K+1)L, so 8 boolean gates fit one
+// SM), accumulating the (K+1) output spectra in registers across levels; BSK_i is read once per CTA and feeds G gates,
+// and its loads are issued before the barrier they would otherwise wait behind.
+#pragma once
+#include "pbs_kernel.cuh"
+
+namespace hb {
+
+__device__ __forceinline__ double2 ldg_nc(const double2* p) {
+    double2 v;
+    asm volatile("ld.global.nc.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p));
+    return v;
+}
+
+template <class T, int K, int L, int G>
+struct Pbs16Cfg {
+    static constexpr int N = 512, M = 256, R = 16;
+    static constexpr int NT = G * (K + 1) * R;
+    static constexpr int XROW = R * (R + 1);               // one spectrum: [k0][j0], rows padded to 17 double2
+    static constexpr int APAD = N + 16;                    // accumulator polynomial stride: odd polynomials land on the other 16 banks
+    static constexpr int REM = M > NT ? M - NT : 0;        // positions not covered by "one position per thread"
+    static_assert(NT >= M || REM * (K + 1) == NT, "MAC split needs NT >= M or (M - NT)(K+1) == NT");
+    static_assert(NT % 32 == 0, "whole warps");
+    __host__ __device__ static constexpr size_t smem_bytes(int n) {
+        return (size_t)G * (K + 1) * XROW * sizeof(double2) + 2 * (size_t)M * sizeof(double2) +
+               (size_t)G * (K + 1) * APAD * sizeof(T) + (((size_t)G * (n + 1) * 2 + 15) & ~(size_t)15);
+    }
+};
+
+template <class T, int K, int L, int G, int MINB>
+__global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const PbsArgs A) {
+    using C = Pbs16Cfg<T, K, L, G>;
+    constexpr int N = C::N, M = C::M, R = 16, NT = C::NT, XROW = C::XROW, APAD = C::APAD, ROWS = (K + 1) * L;
+    constexpr int TWA = HB_TW_DEN / (4 * R);
+    using Dig = DigPack<sizeof(T) == 4>;
+    using DigT = typename Dig::type;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double2* X = reinterpret_cast<double2*>(smem_raw);                  // [G][K+1][XROW]
+    double2* WA = X + (size_t)G * (K + 1) * XROW;                       // W(j0,k0) at k0*16+j0
+    double2* WB = WA + M;                                               // W(j0,k0) at j0*16+k0
+    T* acc = reinterpret_cast<T*>(WB + M);                              // [G][K+1][APAD]
+    uint16_t* atil = reinterpret_cast<uint16_t*>(acc + (size_t)G * (K + 1) * APAD);   // [G][n+1]
+
+    const int tid = threadIdx.x;
+    const int n = A.n;
+    const int job0 = blockIdx.x * G;
+    const T* in = reinterpret_cast<const T*>(A.in);
+
+    for (int x = tid; x < 2 * M; x += NT) WA[x] = A.wtab[x];
+    // ---- prologue: linear combination + modulus switch (App. A.5)
+    for (int g = 0; g < G; ++g) {
+        const int jid = job0 + g;
+        if (jid >= (int)A.n_jobs) { for (int x = tid; x <= n; x += NT) atil[g * (n + 1) + x] = 0; continue; }
+        const PbsJob jb = A.jobs[jid];
+        const T* s0 = in + (size_t)jb.src0 * A.in_stride;
+        const T* s1 = in + (size_t)jb.src1 * A.in_stride;
+        for (int x = tid; x <= n; x += NT) {
+            T v = 0;
+            if (jb.c0) v += (T)(int64_t)jb.c0 * s0[x];
+            if (jb.c1) v += (T)(int64_t)jb.c1 * s1[x];
+            if (x == n) v += (T)jb.cst;
+            const T sh = v >> (TorusOps<T>::BITS - ilog2c(N) - 2);
+            atil[g * (n + 1) + x] = (uint16_t)(((sh + 1) >> 1) & (2 * N - 1));
+        }
+    }
+    __syncthreads();
+    // ---- accumulator = TV * X^{-b~}
+    for (int g = 0; g < G; ++g) {
+        const int jid = job0 + g;
+        T* ag = acc + (size_t)g * (K + 1) * APAD;
+        if (jid >= (int)A.n_jobs) { for (int x = tid; x < (K + 1) * APAD; x += NT) ag[x] = 0; continue; }
+        const PbsJob jb = A.jobs[jid];
+        const int bt = atil[g * (n + 1) + n];
+        const int a0 = (2 * N - bt) & (2 * N - 1);
+        for (int x = tid; x < K * APAD; x += NT) ag[x] = 0;
+        for (int c = tid; c < N; c += NT) {
+            int t = c - a0; if (t < 0) t += 2 * N;
+            const T v = t < N ? tv_body<T>(jb, N, t) : (T)(0 - tv_body<T>(jb, N, t - N));
+            ag[K * APAD + c] = v;
+        }
+    }
+    __syncthreads();
+
+    // ---- roles
+    const int idx = tid & 15;                 // j0 in the first FFT stage, k0 in the second
+    const int gr = tid >> 4;                  // g*(K+1) + r
+    const int g_own = gr / (K + 1);
+    T* ap = acc + (size_t)gr * APAD;          // this half-warp's accumulator polynomial
+    double2* xr = X + (size_t)gr * XROW;      // and its spectrum buffer
+    // MAC roles: one position for every gate and every output polynomial, plus (when NT < M) one (position, output
+    // polynomial) pair of the remaining positions for every gate
+    const bool has1 = tid < M;
+    const int pos1 = tid < M ? tid : 0;
+    const int s1 = (pos1 >> 4) * (R + 1) + (pos1 & 15);
+    constexpr bool HAS2 = C::REM > 0;
+    const int pos2 = HAS2 ? NT + tid % (HAS2 ? C::REM : 1) : 0;
+    const int j2 = HAS2 ? tid / (HAS2 ? C::REM : 1) : 0;
+    const int s2 = (pos2 >> 4) * (R + 1) + (pos2 & 15);
+
+    for (int i = 0; i < n; ++i) {
+        int any = 0;
+#pragma unroll
+        for (int g = 0; g < G; ++g) any |= atil[g * (n + 1) + i];
+        if (any == 0) continue;                       // uniform across the CTA
+
+        // A: rotate-subtract and signed decomposition of this thread's 32 coefficients, all L levels at once
+        DigT pk[L][R / 2];
+        {
+            const int a = atil[g_own * (n + 1) + i];
+#pragma unroll
+            for (int part = 0; part < R / 2; ++part) {
+                int32_t dg[4][L];
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    const int c = idx + R * (2 * part + u);
+                    digits_all<T, L>(rot_read<T>(ap, N, c, a) - ap[c], A.base_log, dg[2 * u]);
+                    digits_all<T, L>(rot_read<T>(ap, N, c + M, a) - ap[c + M], A.base_log, dg[2 * u + 1]);
+                }
+#pragma unroll
+                for (int lev = 0; lev < L; ++lev) pk[lev][part] = Dig::make(dg[0][lev], dg[1][lev], dg[2][lev], dg[3][lev]);
+            }
+        }
+        double2 o1[G][K + 1];
+        double2 o2[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            o2[g] = make_double2(0.0, 0.0);
+#pragma unroll
+            for (int j = 0; j <= K; ++j) o1[g][j] = make_double2(0.0, 0.0);
+        }
+
+#pragma unroll
+        for (int lev = 0; lev < L; ++lev) {
+            // B: twist, radix-16 DFT over j1, inter-stage twiddle -> row-major spectrum buffer
+            {
+                double2 x[R];
+#pragma unroll
+                for (int part = 0; part < R / 2; ++part) {
+                    const DigT p = pk[lev][part];
+                    x[2 * part] = cmul_tw<1>(make_double2(Dig::template get<0>(p), Dig::template get<1>(p)), (2 * part) * TWA);
+                    x[2 * part + 1] = cmul_tw<1>(make_double2(Dig::template get<2>(p), Dig::template get<3>(p)), (2 * part + 1) * TWA);
+                }
+                dft_regs<R, 1>(x);
+#pragma unroll
+                for (int k0 = 0; k0 < R; ++k0) xr[k0 * (R + 1) + idx] = cmul(x[brev<R>(k0)], WA[k0 * R + idx]);
+            }
+            __syncwarp();
+            // C: radix-16 DFT over j0 of column k0 = idx, in place
+            {
+                double2* xc = xr + idx * (R + 1);
+                double2 x[R];
+#pragma unroll
+                for (int j0 = 0; j0 < R; ++j0) x[j0] = xc[j0];
+                dft_regs<R, 1>(x);
+#pragma unroll
+                for (int k1 = 0; k1 < R; ++k1) xc[k1] = x[brev<R>(k1)];
+            }
+            // D: pointwise MAC of this level's (K+1) spectra per gate with rows lev*(K+1)+r of BSK_i.  The key loads do
+            // not depend on the spectra: issue them before the barrier.
+            const double2* bp = A.bsk + ((size_t)i * ROWS + lev * (K + 1)) * (K + 1) * M;
+            double2 b1[K + 1][K + 1];
+            double2 b2[K + 1];
+#pragma unroll
+            for (int r = 0; r <= K; ++r) {
+#pragma unroll
+                for (int j = 0; j <= K; ++j) b1[r][j] = ldg_nc(bp + (size_t)(r * (K + 1) + j) * M + pos1);
+                if (HAS2) b2[r] = ldg_nc(bp + (size_t)(r * (K + 1) + j2) * M + pos2);
+            }
+            __syncthreads();
+            if (has1) {
+#pragma unroll
+                for (int r = 0; r <= K; ++r) {
+#pragma unroll
+                    for (int g = 0; g < G; ++g) {
+                        const double2 f = X[((size_t)g * (K + 1) + r) * XROW + s1];
+#pragma unroll
+                        for (int j = 0; j <= K; ++j) cfma(o1[g][j], f, b1[r][j]);
+                    }
+                }
+            }
+            if (HAS2) {
+#pragma unroll
+                for (int r = 0; r <= K; ++r) {
+#pragma unroll
+                    for (int g = 0; g < G; ++g) cfma(o2[g], X[((size_t)g * (K + 1) + r) * XROW + s2], b2[r]);
+                }
+            }
+            __syncthreads();
+        }
+        // output spectra -> the buffers of the polynomials they belong to
+        if (has1) {
+#pragma unroll
+            for (int g = 0; g < G; ++g)
+#pragma unroll
+                for (int j = 0; j <= K; ++j) X[((size_t)g * (K + 1) + j) * XROW + s1] = o1[g][j];
+        }
+        if (HAS2) {
+#pragma unroll
+            for (int g = 0; g < G; ++g) X[((size_t)g * (K + 1) + j2) * XROW + s2] = o2[g];
+        }
+        __syncthreads();
+        // E: inverse radix-16 DFT over k1 of column k0 = idx, conj inter-stage twiddle
+        {
+            double2* xc = xr + idx * (R + 1);
+            double2 x[R];
+#pragma unroll
+            for (int k1 = 0; k1 < R; ++k1) x[k1] = xc[k1];
+            dft_regs<R, -1>(x);
+#pragma unroll
+            for (int j0 = 0; j0 < R; ++j0) xc[j0] = cmul_conj(x[brev<R>(j0)], WB[j0 * R + idx]);
+        }
+        __syncwarp();
+        // F: inverse radix-16 DFT over k0, untwist, round, wrapping add into the accumulator
+        {
+            double2 x[R];
+#pragma unroll
+            for (int k0 = 0; k0 < R; ++k0) x[k0] = xr[k0 * (R + 1) + idx];
+            dft_regs<R, -1>(x);
+#pragma unroll
+            for (int j1 = 0; j1 < R; ++j1) {
+                const double2 z = cmul_tw<-1>(x[brev<R>(j1)], j1 * TWA);
+                const int c = idx + R * j1;
+                ap[c] += TorusOps<T>::round_add(z.x);
+                ap[c + M] += TorusOps<T>::round_add(z.y);
+            }
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+
+    // ---- epilogue: sample extract coefficient 0 (App. A.5)
+    T* out = reinterpret_cast<T*>(A.out);
+    for (int g = 0; g < G; ++g) {
+        const int jid = job0 + g;
+        if (jid >= (int)A.n_jobs) continue;
+        const uint32_t dst = A.jobs[jid].dst;
+        const T* ag = acc + (size_t)g * (K + 1) * APAD;
+        T* o = out + (size_t)dst * A.out_stride;
+        for (int x = tid; x < K * N; x += NT) {
+            const int j = x / N, c = x % N;
+            o[x] = c == 0 ? ag[j * APAD] : (T)(0 - ag[j * APAD + N - c]);
+        }
+        if (tid == 0) o[K * N] = ag[K * APAD];
+    }
+}
+
+}  // namespace hb
