@@ -121,6 +121,7 @@ struct Shape {
     size_t (*smem)(int n);
     cudaError_t (*launch)(const PbsArgs&, cudaStream_t, size_t smem);
     cudaError_t (*bsk_fft)(const void* std_bsk, double2* out, const double2* wtab, size_t polys, cudaStream_t);
+    int BL = 0;                            // compile-time pbs_base_log of the instance (0: run-time)
 };
 
 template <class T, int N, int K, int L, int RA, int RB, int G, int NT, int MINB>
@@ -148,12 +149,12 @@ struct Inst {
 };
 
 // N = 512 shapes run the half-warp-per-polynomial kernel (pbs16_kernel.cuh); the key transform and the Fourier key layout are shared
-template <class T, int K, int L, int G, int MINB>
+template <class T, int K, int L, int BL, int G, int MINB>
 struct Inst16 {
     using C = Pbs16Cfg<T, K, L, G>;
     static size_t smem(int n) { return C::smem_bytes(n); }
     static cudaError_t launch(const PbsArgs& a, cudaStream_t s, size_t smem) {
-        auto kern = pbs16_kernel<T, K, L, G, MINB>;
+        auto kern = pbs16_kernel<T, K, L, BL, G, MINB>;
         static bool attr_done = false;
         if (!attr_done) {
             cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
@@ -164,14 +165,14 @@ struct Inst16 {
         kern<<<grid, C::NT, smem, s>>>(a);
         return cudaGetLastError();
     }
-    static constexpr Shape shape() { return Shape{(int)sizeof(T) * 8, 512, K, L, 16, 16, G, C::NT, &smem, &launch, &Inst<T, 512, K, L, 16, 16, 1, 32, 1>::bsk_fft}; }
+    static constexpr Shape shape() { return Shape{(int)sizeof(T) * 8, 512, K, L, 16, 16, G, C::NT, &smem, &launch, &Inst<T, 512, K, L, 16, 16, 1, 32, 1>::bsk_fft, BL}; }
 };
 
 const Shape g_shapes[] = {
 #ifdef HB_PBS_V2
     Inst<uint32_t, 512, 2, 3, 16, 16, 2, 288, 2>::shape(),     // tfhe boolean DEFAULT_PARAMETERS
 #else
-    Inst16<uint32_t, 2, 3, 4, 2>::shape(),                     // tfhe boolean DEFAULT_PARAMETERS
+    Inst16<uint32_t, 2, 3, 6, 4, 2>::shape(),                  // tfhe boolean DEFAULT_PARAMETERS
 #endif
     Inst<uint32_t, 1024, 1, 3, 16, 32, 1, 192, 2>::shape(),    // concrete-core GPU path of the reference
     Inst<uint64_t, 512, 3, 1, 16, 16, 2, 128, 2>::shape(),     // PARAM_MESSAGE_1_CARRY_1_KS_PBS
@@ -181,7 +182,7 @@ const Shape g_shapes[] = {
 int find_shape(const hb_params& p) {
     for (size_t i = 0; i < sizeof(g_shapes) / sizeof(g_shapes[0]); ++i) {
         const Shape& s = g_shapes[i];
-        if (s.bits == p.torus_bits && s.N == p.N && s.K == p.k && s.L == p.pbs_level) return (int)i;
+        if (s.bits == p.torus_bits && s.N == p.N && s.K == p.k && s.L == p.pbs_level && (s.BL == 0 || s.BL == p.pbs_base_log)) return (int)i;
     }
     return -1;
 }

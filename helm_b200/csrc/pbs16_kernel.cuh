@@ -10,7 +10,12 @@
 // with __syncwarp() only.  The single CTA-wide exchange is the pointwise MAC with BSK_i, which mixes polynomials:
 // it is done level by level ((K+1) spectra per gate in shared memory instead of (K+1)L, so 8 boolean gates fit one
 // SM), accumulating the (K+1) output spectra in registers across levels; BSK_i is read once per CTA and feeds G gates,
-// and its loads are issued before the barrier they would otherwise wait behind.
+// and its loads are issued before the barrier they would otherwise wait behind.  The "spectra consumed" side of that
+// exchange is a split arrive / wait (mbarrier), so the next level's register-resident DFT overlaps other warps' MAC.
+//
+// u32 torus: the accumulator is kept as its negacyclic extension E[t], t in [0, 2N), E[t+N] = -E[t], so the rotated
+// read X^a * acc is E[(c - a) mod 2N] with no sign logic, and the signed decomposition uses a closed form of the
+// tfhe-rs carry rule with compile-time base_log (profiles/r01_v3_*: the integer ALU pipe bounded that phase).
 #pragma once
 #include "pbs_kernel.cuh"
 
@@ -21,42 +26,76 @@ __device__ __forceinline__ double2 ldg_nc(const double2* p) {
     asm volatile("ld.global.nc.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p));
     return v;
 }
+__device__ __forceinline__ void mbar_init(uint32_t addr, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(addr), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t addr) {
+    asm volatile("{ .reg .b64 st; mbarrier.arrive.shared::cta.b64 st, [%0]; }" ::"r"(addr) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t addr, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                     : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
+    } while (!ok);
+}
+
+// Signed decomposition of a u32 torus value into L biased bytes (digit + 64), closed form of tfhe-rs
+// SignedDecomposer (App. A.3): with b = bit (BL-1) of the next residue, carry = (res + 2^(BL-1) - 1 + b) >> BL, hence
+// u = state + 2^(BL-1) - 1 + b gives digit = (u mod 2^BL) - (2^(BL-1) - 1) - b and next state = u >> BL.
+// xr = value + 2^(31 - BL*L) (the closest-representable rounding add; the caller folds it into the rotate-subtract).
+// Checked exhaustively against digits_all (tests/test_oracle_kat.py restates it on the CPU side).
+template <int BL, int L> __device__ __forceinline__ void digit_bytes_u32(uint32_t xr, uint32_t (&byte)[L]) {
+    static_assert(BL * L < 32 && BL <= 7, "byte-staged digits");
+    constexpr uint32_t HALF1 = (1u << (BL - 1)) - 1, MASK = (1u << BL) - 1;
+    uint32_t s = xr >> (32 - BL * L);
+#pragma unroll
+    for (int l = L - 1; l >= 0; --l) {
+        const uint32_t b = (s >> (2 * BL - 1)) & 1u;
+        const uint32_t u = s + HALF1 + b;
+        byte[l] = (u & MASK) + (64u - HALF1) - b;
+        s = u >> BL;
+    }
+}
 
 template <class T, int K, int L, int G>
 struct Pbs16Cfg {
     static constexpr int N = 512, M = 256, R = 16;
     static constexpr int NT = G * (K + 1) * R;
     static constexpr int XROW = R * (R + 1);               // one spectrum: [k0][j0], rows padded to 17 double2
-    static constexpr int APAD = N + 16;                    // accumulator polynomial stride: odd polynomials land on the other 16 banks
+    static constexpr bool EXT = sizeof(T) == 4;            // negacyclic-extended accumulator (2N words per polynomial)
+    static constexpr int ASTRIDE = EXT ? 2 * N : N + 16;   // non-extended: odd polynomials land on the other 16 banks
     static constexpr int REM = M > NT ? M - NT : 0;        // positions not covered by "one position per thread"
     static_assert(NT >= M || REM * (K + 1) == NT, "MAC split needs NT >= M or (M - NT)(K+1) == NT");
     static_assert(NT % 32 == 0, "whole warps");
     __host__ __device__ static constexpr size_t smem_bytes(int n) {
-        return (size_t)G * (K + 1) * XROW * sizeof(double2) + 2 * (size_t)M * sizeof(double2) +
-               (size_t)G * (K + 1) * APAD * sizeof(T) + (((size_t)G * (n + 1) * 2 + 15) & ~(size_t)15);
+        return (size_t)G * (K + 1) * XROW * sizeof(double2) + (size_t)XROW * sizeof(double2) +
+               (size_t)G * (K + 1) * ASTRIDE * sizeof(T) + (((size_t)G * (n + 1) * 2 + 15) & ~(size_t)15) + 16;
     }
 };
 
-template <class T, int K, int L, int G, int MINB>
+template <class T, int K, int L, int BL, int G, int MINB>
 __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const PbsArgs A) {
     using C = Pbs16Cfg<T, K, L, G>;
-    constexpr int N = C::N, M = C::M, R = 16, NT = C::NT, XROW = C::XROW, APAD = C::APAD, ROWS = (K + 1) * L;
+    constexpr int N = C::N, M = C::M, R = 16, NT = C::NT, XROW = C::XROW, AS = C::ASTRIDE, ROWS = (K + 1) * L;
     constexpr int TWA = HB_TW_DEN / (4 * R);
+    constexpr bool EXT = C::EXT;
     using Dig = DigPack<sizeof(T) == 4>;
     using DigT = typename Dig::type;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double2* X = reinterpret_cast<double2*>(smem_raw);                  // [G][K+1][XROW]
-    double2* WA = X + (size_t)G * (K + 1) * XROW;                       // W(j0,k0) at k0*16+j0
-    double2* WB = WA + M;                                               // W(j0,k0) at j0*16+k0
-    T* acc = reinterpret_cast<T*>(WB + M);                              // [G][K+1][APAD]
-    uint16_t* atil = reinterpret_cast<uint16_t*>(acc + (size_t)G * (K + 1) * APAD);   // [G][n+1]
+    double2* W = X + (size_t)G * (K + 1) * XROW;                        // W(j0,k0) at k0*17+j0
+    T* acc = reinterpret_cast<T*>(W + XROW);                            // [G][K+1][AS]
+    uint16_t* atil = reinterpret_cast<uint16_t*>(acc + (size_t)G * (K + 1) * AS);   // [G][n+1]
 
     const int tid = threadIdx.x;
     const int n = A.n;
     const int job0 = blockIdx.x * G;
     const T* in = reinterpret_cast<const T*>(A.in);
+    const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(atil) + (uint32_t)((((size_t)G * (n + 1) * 2 + 15) & ~(size_t)15));
+    if (tid == 0) mbar_init(mbar, NT);
 
-    for (int x = tid; x < 2 * M; x += NT) WA[x] = A.wtab[x];
+    for (int x = tid; x < M; x += NT) W[(x >> 4) * (R + 1) + (x & 15)] = A.wtab[x];
     // ---- prologue: linear combination + modulus switch (App. A.5)
     for (int g = 0; g < G; ++g) {
         const int jid = job0 + g;
@@ -77,16 +116,17 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
     // ---- accumulator = TV * X^{-b~}
     for (int g = 0; g < G; ++g) {
         const int jid = job0 + g;
-        T* ag = acc + (size_t)g * (K + 1) * APAD;
-        if (jid >= (int)A.n_jobs) { for (int x = tid; x < (K + 1) * APAD; x += NT) ag[x] = 0; continue; }
+        T* ag = acc + (size_t)g * (K + 1) * AS;
+        if (jid >= (int)A.n_jobs) { for (int x = tid; x < (K + 1) * AS; x += NT) ag[x] = 0; continue; }
         const PbsJob jb = A.jobs[jid];
         const int bt = atil[g * (n + 1) + n];
         const int a0 = (2 * N - bt) & (2 * N - 1);
-        for (int x = tid; x < K * APAD; x += NT) ag[x] = 0;
+        for (int x = tid; x < K * AS; x += NT) ag[x] = 0;
         for (int c = tid; c < N; c += NT) {
             int t = c - a0; if (t < 0) t += 2 * N;
             const T v = t < N ? tv_body<T>(jb, N, t) : (T)(0 - tv_body<T>(jb, N, t - N));
-            ag[K * APAD + c] = v;
+            ag[K * AS + c] = v;
+            if (EXT) ag[K * AS + N + c] = (T)(0 - v);
         }
     }
     __syncthreads();
@@ -95,7 +135,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
     const int idx = tid & 15;                 // j0 in the first FFT stage, k0 in the second
     const int gr = tid >> 4;                  // g*(K+1) + r
     const int g_own = gr / (K + 1);
-    T* ap = acc + (size_t)gr * APAD;          // this half-warp's accumulator polynomial
+    T* ap = acc + (size_t)gr * AS;            // this half-warp's accumulator polynomial
     double2* xr = X + (size_t)gr * XROW;      // and its spectrum buffer
     // MAC roles: one position for every gate and every output polynomial, plus (when NT < M) one (position, output
     // polynomial) pair of the remaining positions for every gate
@@ -103,9 +143,11 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
     const int pos1 = tid < M ? tid : 0;
     const int s1 = (pos1 >> 4) * (R + 1) + (pos1 & 15);
     constexpr bool HAS2 = C::REM > 0;
-    const int pos2 = HAS2 ? NT + tid % (HAS2 ? C::REM : 1) : 0;
-    const int j2 = HAS2 ? tid / (HAS2 ? C::REM : 1) : 0;
+    constexpr int REM1 = HAS2 ? C::REM : 1;
+    const int pos2 = HAS2 ? NT + tid % REM1 : 0;
+    const int j2 = HAS2 ? tid / REM1 : 0;
     const int s2 = (pos2 >> 4) * (R + 1) + (pos2 & 15);
+    uint32_t parity = 0;
 
     for (int i = 0; i < n; ++i) {
         int any = 0;
@@ -113,21 +155,41 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
         for (int g = 0; g < G; ++g) any |= atil[g * (n + 1) + i];
         if (any == 0) continue;                       // uniform across the CTA
 
-        // A: rotate-subtract and signed decomposition of this thread's 32 coefficients, all L levels at once
+        // A: rotate-subtract and signed decomposition of this thread's 32 coefficients c = idx + 16 m, all L levels.
+        // pk[lev][part] packs the digits of coefficients (c, c+M) for j1 = 2 part and 2 part + 1 (DigPack order).
         DigT pk[L][R / 2];
         {
             const int a = atil[g_own * (n + 1) + i];
+            if constexpr (EXT) {
+                const uint32_t b4 = (uint32_t)((idx - a) & (2 * N - 1)) << 2;     // byte offset of E[(idx - a) mod 2N]
+                const unsigned char* eb = reinterpret_cast<const unsigned char*>(ap);
+                constexpr uint32_t RND = 1u << (31 - BL * L);
 #pragma unroll
-            for (int part = 0; part < R / 2; ++part) {
-                int32_t dg[4][L];
+                for (int part = 0; part < R / 2; ++part) {
+                    uint32_t by[4][L];
 #pragma unroll
-                for (int u = 0; u < 2; ++u) {
-                    const int c = idx + R * (2 * part + u);
-                    digits_all<T, L>(rot_read<T>(ap, N, c, a) - ap[c], A.base_log, dg[2 * u]);
-                    digits_all<T, L>(rot_read<T>(ap, N, c + M, a) - ap[c + M], A.base_log, dg[2 * u + 1]);
+                    for (int u = 0; u < 4; ++u) {
+                        const int m = 2 * part + (u >> 1) + 16 * (u & 1);        // u: (c), (c+M), (c+16), (c+16+M)
+                        const uint32_t rot = *reinterpret_cast<const uint32_t*>(eb + ((b4 + 64u * m) & (8u * N - 1)));
+                        digit_bytes_u32<BL, L>(rot - (uint32_t)ap[idx + R * m] + RND, by[u]);
+                    }
+#pragma unroll
+                    for (int lev = 0; lev < L; ++lev)
+                        pk[lev][part] = by[0][lev] + (by[1][lev] << 8) + (by[2][lev] << 16) + (by[3][lev] << 24);
                 }
+            } else {
 #pragma unroll
-                for (int lev = 0; lev < L; ++lev) pk[lev][part] = Dig::make(dg[0][lev], dg[1][lev], dg[2][lev], dg[3][lev]);
+                for (int part = 0; part < R / 2; ++part) {
+                    int32_t dg[4][L];
+#pragma unroll
+                    for (int u = 0; u < 2; ++u) {
+                        const int c = idx + R * (2 * part + u);
+                        digits_all<T, L>(rot_read<T>(ap, N, c, a) - ap[c], BL, dg[2 * u]);
+                        digits_all<T, L>(rot_read<T>(ap, N, c + M, a) - ap[c + M], BL, dg[2 * u + 1]);
+                    }
+#pragma unroll
+                    for (int lev = 0; lev < L; ++lev) pk[lev][part] = Dig::make(dg[0][lev], dg[1][lev], dg[2][lev], dg[3][lev]);
+                }
             }
         }
         double2 o1[G][K + 1];
@@ -139,20 +201,25 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
             for (int j = 0; j <= K; ++j) o1[g][j] = make_double2(0.0, 0.0);
         }
 
-#pragma unroll
+#pragma unroll 1
         for (int lev = 0; lev < L; ++lev) {
-            // B: twist, radix-16 DFT over j1, inter-stage twiddle -> row-major spectrum buffer
+            // B: twist, radix-16 DFT over j1, inter-stage twiddle (all in registers) ...
             {
                 double2 x[R];
 #pragma unroll
                 for (int part = 0; part < R / 2; ++part) {
-                    const DigT p = pk[lev][part];
+                    const DigT p = pk[0][part];
                     x[2 * part] = cmul_tw<1>(make_double2(Dig::template get<0>(p), Dig::template get<1>(p)), (2 * part) * TWA);
                     x[2 * part + 1] = cmul_tw<1>(make_double2(Dig::template get<2>(p), Dig::template get<3>(p)), (2 * part + 1) * TWA);
                 }
                 dft_regs<R, 1>(x);
+                double2 y[R];
 #pragma unroll
-                for (int k0 = 0; k0 < R; ++k0) xr[k0 * (R + 1) + idx] = cmul(x[brev<R>(k0)], WA[k0 * R + idx]);
+                for (int k0 = 0; k0 < R; ++k0) y[k0] = cmul(x[brev<R>(k0)], W[k0 * (R + 1) + idx]);
+                // ... then wait until every thread has consumed the previous level's spectra, and publish the row
+                if (lev > 0) { mbar_wait(mbar, parity); parity ^= 1u; }
+#pragma unroll
+                for (int k0 = 0; k0 < R; ++k0) xr[k0 * (R + 1) + idx] = y[k0];
             }
             __syncwarp();
             // C: radix-16 DFT over j0 of column k0 = idx, in place
@@ -195,9 +262,14 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
                     for (int g = 0; g < G; ++g) cfma(o2[g], X[((size_t)g * (K + 1) + r) * XROW + s2], b2[r]);
                 }
             }
-            __syncthreads();
+            mbar_arrive(mbar);                       // this thread no longer reads this level's spectra
+#pragma unroll
+            for (int l = 0; l + 1 < L; ++l)
+#pragma unroll
+                for (int part = 0; part < R / 2; ++part) pk[l][part] = pk[l + 1][part];
         }
-        // output spectra -> the buffers of the polynomials they belong to
+        // output spectra -> the buffers of the polynomials they belong to (once everyone is done reading them)
+        mbar_wait(mbar, parity); parity ^= 1u;
         if (has1) {
 #pragma unroll
             for (int g = 0; g < G; ++g)
@@ -217,7 +289,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
             for (int k1 = 0; k1 < R; ++k1) x[k1] = xc[k1];
             dft_regs<R, -1>(x);
 #pragma unroll
-            for (int j0 = 0; j0 < R; ++j0) xc[j0] = cmul_conj(x[brev<R>(j0)], WB[j0 * R + idx]);
+            for (int j0 = 0; j0 < R; ++j0) xc[j0] = cmul_conj(x[brev<R>(j0)], W[idx * (R + 1) + j0]);
         }
         __syncwarp();
         // F: inverse radix-16 DFT over k0, untwist, round, wrapping add into the accumulator
@@ -230,8 +302,10 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
             for (int j1 = 0; j1 < R; ++j1) {
                 const double2 z = cmul_tw<-1>(x[brev<R>(j1)], j1 * TWA);
                 const int c = idx + R * j1;
-                ap[c] += TorusOps<T>::round_add(z.x);
-                ap[c + M] += TorusOps<T>::round_add(z.y);
+                const T v0 = ap[c] + TorusOps<T>::round_add(z.x);
+                const T v1 = ap[c + M] + TorusOps<T>::round_add(z.y);
+                ap[c] = v0; ap[c + M] = v1;
+                if constexpr (EXT) { ap[c + N] = (T)(0 - v0); ap[c + M + N] = (T)(0 - v1); }
             }
         }
         __syncwarp();
@@ -244,13 +318,13 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
         const int jid = job0 + g;
         if (jid >= (int)A.n_jobs) continue;
         const uint32_t dst = A.jobs[jid].dst;
-        const T* ag = acc + (size_t)g * (K + 1) * APAD;
+        const T* ag = acc + (size_t)g * (K + 1) * AS;
         T* o = out + (size_t)dst * A.out_stride;
         for (int x = tid; x < K * N; x += NT) {
             const int j = x / N, c = x % N;
-            o[x] = c == 0 ? ag[j * APAD] : (T)(0 - ag[j * APAD + N - c]);
+            o[x] = c == 0 ? ag[j * AS] : (T)(0 - ag[j * AS + N - c]);
         }
-        if (tid == 0) o[K * N] = ag[K * APAD];
+        if (tid == 0) o[K * N] = ag[K * AS];
     }
 }
 
