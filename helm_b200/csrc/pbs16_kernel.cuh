@@ -64,7 +64,7 @@ struct Pbs16Cfg {
     static constexpr int NT = G * (K + 1) * R;
     static constexpr int XROW = R * (R + 1);               // one spectrum: [k0][j0], rows padded to 17 double2
     static constexpr bool EXT = sizeof(T) == 4;            // negacyclic-extended accumulator (2N words per polynomial)
-    static constexpr int ASTRIDE = EXT ? 2 * N : N + 16;   // non-extended: odd polynomials land on the other 16 banks
+    static constexpr int ASTRIDE = (EXT ? 2 * N : N) + 16;  // +16 words: odd polynomials land on the other 16 banks
     static constexpr int REM = M > NT ? M - NT : 0;        // positions not covered by "one position per thread"
     static_assert(NT >= M || REM * (K + 1) == NT, "MAC split needs NT >= M or (M - NT)(K+1) == NT");
     static_assert(NT % 32 == 0, "whole warps");
