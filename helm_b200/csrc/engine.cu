@@ -105,6 +105,21 @@ template <class T> __global__ void linear_rows(T* w, uint32_t stride, const LinJ
     }
 }
 
+// dst = sum_s c[s]*src[s] + cst(body), up to 4 sources (job layout shared with the keyswitch prologue)
+template <class T> __global__ void lincomb_rows(T* w, uint32_t stride, const KsJob* jobs, uint32_t cnt, uint32_t words) {
+    for (uint32_t r = blockIdx.y; r < cnt; r += gridDim.y) {
+        const KsJob j = jobs[r];
+        T* d = w + (size_t)j.dst * stride;
+        for (uint32_t x = blockIdx.x * blockDim.x + threadIdx.x; x < words; x += gridDim.x * blockDim.x) {
+            T v = 0;
+#pragma unroll
+            for (int s = 0; s < 4; ++s) if (j.c[s]) v += (T)(int64_t)j.c[s] * w[(size_t)j.src[s] * stride + x];
+            if (x == words - 1) v += (T)j.cst;
+            d[x] = v;
+        }
+    }
+}
+
 __global__ void dfma_peak_kernel(double* out, int iters) {
     double a0 = threadIdx.x * 1e-9, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
     const double b = 1.0000001, c = 1e-7;
@@ -275,6 +290,16 @@ hb_status launch_lin(hb_ctx* c, void* w, uint32_t stride, const LinJob* jobs, ui
     dim3 grid((words + 255) / 256, cnt < 32768 ? cnt : 32768);
     if (c->p.torus_bits == 32) linear_rows<uint32_t><<<grid, 256, 0, c->stream>>>((uint32_t*)w, stride, jobs, cnt, words);
     else linear_rows<uint64_t><<<grid, 256, 0, c->stream>>>((uint64_t*)w, stride, jobs, cnt, words);
+    CU(c, cudaGetLastError());
+    c->stats.kernel_launches++;
+    return HB_OK;
+}
+
+hb_status launch_lincomb(hb_ctx* c, void* w, uint32_t stride, const KsJob* jobs, uint32_t cnt, uint32_t words) {
+    if (!cnt) return HB_OK;
+    dim3 grid((words + 255) / 256, cnt < 32768 ? cnt : 32768);
+    if (c->p.torus_bits == 32) lincomb_rows<uint32_t><<<grid, 256, 0, c->stream>>>((uint32_t*)w, stride, jobs, cnt, words);
+    else lincomb_rows<uint64_t><<<grid, 256, 0, c->stream>>>((uint64_t*)w, stride, jobs, cnt, words);
     CU(c, cudaGetLastError());
     c->stats.kernel_launches++;
     return HB_OK;
@@ -672,6 +697,57 @@ hb_status hb_eval_level(hb_ctx* c, hb_wires* w, const hb_gate* gates, uint32_t n
     slot->first_is_pbs = p.order == 0; slot->pending = true;
     if (hb_status s = launch_lin(c, w->dev, wstride, dl, (uint32_t)lj.size(), ct_words(c))) return s;
     CU(c, cudaEventRecord(slot->done, c->stream));
+    c->stats.levels++;
+    return HB_OK;
+}
+
+hb_status hb_eval_shortint_ops(hb_ctx* c, hb_wires* w, const hb_sop* ops, uint32_t n_ops) {
+    if (hb_status s = check_ready(c)) return s;
+    if (!w || w->ctx != c || (!ops && n_ops)) return fail(c, HB_ERR_ARG, "hb_eval_shortint_ops: bad arguments");
+    if (c->p.order != 1) return fail(c, HB_ERR_UNSUPPORTED, "hb_eval_shortint_ops needs a shortint (order 1) parameter set");
+    if (!n_ops) return HB_OK;
+    CU(c, cudaSetDevice(c->device));
+    const hb_params& p = c->p;
+    const int mc = p.msg_mod * p.carry_mod;
+    int lg = 0; while ((1 << lg) < mc) ++lg;
+    const uint64_t delta = 1ull << (p.torus_bits - 1 - lg);
+    std::vector<PbsJob> pj; std::vector<KsJob> kj, lin;
+    for (uint32_t i = 0; i < n_ops; ++i) {
+        const hb_sop& o = ops[i];
+        if (o.n_in > 4 || o.out >= w->n_wires) return fail(c, HB_ERR_ARG, "shortint op: bad arity or output wire");
+        KsJob k{};
+        for (int s = 0; s < o.n_in; ++s) {
+            if (o.in[s] >= w->n_wires) return fail(c, HB_ERR_ARG, "shortint op: input wire out of range");
+            k.src[s] = o.in[s]; k.c[s] = o.coef[s];
+        }
+        k.cst = (uint64_t)((int64_t)o.cst) * delta;
+        if (o.kind == HB_SOP_LINEAR) { k.dst = o.out; lin.push_back(k); }
+        else if (o.kind == HB_SOP_LUT) {
+            k.dst = (uint32_t)kj.size();
+            PbsJob j{}; j.src0 = k.dst; j.c0 = 1; j.dst = o.out; j.tv_kind = 1; j.tv_cst = delta; j.lut_boxes = mc; j.lut = o.table;
+            kj.push_back(k); pj.push_back(j);
+        } else return fail(c, HB_ERR_ARG, "shortint op: unknown kind");
+    }
+    const uint32_t wstride = hb_wire_stride(c);
+    const size_t ts = tsize(c);
+    const PbsJob* dp; const KsJob* dk; const LinJob* dl; JobSlot* slot;
+    if (!pj.empty()) {
+        if (hb_status s = upload_jobs(c, pj, kj, {}, &dp, &dk, &dl, &slot)) return s;
+        const uint32_t sstride = pad4(small_words(c));
+        CU(c, c->scratch_b.ensure((size_t)kj.size() * sstride * ts));
+        CU(c, cudaEventRecord(slot->t[0], c->stream));
+        if (hb_status s = launch_ks(c, w->dev, wstride, c->scratch_b.p, sstride, dk, (uint32_t)kj.size())) return s;
+        CU(c, cudaEventRecord(slot->t[1], c->stream));
+        if (hb_status s = launch_pbs(c, c->scratch_b.p, sstride, w->dev, wstride, dp, (uint32_t)pj.size())) return s;
+        CU(c, cudaEventRecord(slot->t[2], c->stream));
+        slot->first_is_pbs = 0; slot->pending = true;
+        CU(c, cudaEventRecord(slot->done, c->stream));
+    }
+    if (!lin.empty()) {
+        if (hb_status s = upload_jobs(c, {}, lin, {}, &dp, &dk, &dl, &slot)) return s;
+        if (hb_status s = launch_lincomb(c, w->dev, wstride, dk, (uint32_t)lin.size(), ct_words(c))) return s;
+        CU(c, cudaEventRecord(slot->done, c->stream));
+    }
     c->stats.levels++;
     return HB_OK;
 }

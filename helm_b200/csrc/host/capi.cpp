@@ -1,9 +1,11 @@
 // C ABI of the host library (include/helm_host.h).
 #include "../../../include/helm_host.h"
+#include <algorithm>
 #include <chrono>
 #include <cstring>
 #include <sstream>
 #include "eval.hpp"
+#include "arith.hpp"
 
 using namespace helm;
 
@@ -175,6 +177,42 @@ int hh_session_run(hh_session* s, const hh_circuit* c, const char* inputs, int c
         }
         const auto t3 = clk::now();
         if (seconds) { seconds[0] = secs(t0, t1); seconds[1] = secs(t1, t2); seconds[2] = secs(t2, t3); }
+        text = format_values(res);
+    }) || emit(text, buf, cap, needed);
+}
+
+int hh_session_run_arith(hh_session* s, const hh_circuit* c, const char* inputs, const char* ptxt_type, int cycles,
+                         int all_wires, int verbose, char* buf, size_t cap, size_t* needed, double* seconds, uint64_t* counts) {
+    std::string text;
+    return guarded([&] {
+        using clk = std::chrono::steady_clock;
+        auto secs = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double>(b - a).count(); };
+        const Netlist& nl = c->c->netlist();
+        if (!nl.has_arith) throw Error("hh_session_run_arith needs an arithmetic netlist");
+        const std::string pt = ptxt_type ? ptxt_type : "u32";
+        ArithCircuit ev(s->ck, *s->sk, *c->c, ptxt_type_bits(pt));
+        ev.quiet = !verbose;
+        const WireValues in = parse_values(inputs, pt);
+        const auto t0 = clk::now();
+        auto enc = ev.encrypt_inputs(nl.wire_set, in);
+        const bool ready = cycles > 1 && enc->contains("READY");
+        if (ready) ev.init_ready(*enc);
+        const auto t1 = clk::now();
+        for (int cy = 0; cy < (cycles < 1 ? 1 : cycles); ++cy) {
+            ev.evaluate_encrypted(*enc, 1, pt);
+            if (ready) ev.evaluate_ready(*enc);
+        }
+        const auto t2 = clk::now();
+        WireValues res = ev.decrypt_outputs(*enc, verbose != 0, ready);
+        if (all_wires) {
+            std::vector<std::string> names(nl.wire_set.begin(), nl.wire_set.end());
+            for (const auto& w : nl.inputs) if (!nl.wire_set.count(w)) names.push_back(w);
+            std::sort(names.begin(), names.end()); names.erase(std::unique(names.begin(), names.end()), names.end());
+            for (const auto& kv : ev.decrypt_wires(*enc, names)) res[kv.first] = kv.second;
+        }
+        const auto t3 = clk::now();
+        if (seconds) { seconds[0] = secs(t0, t1); seconds[1] = secs(t1, t2); seconds[2] = secs(t2, t3); }
+        if (counts) { counts[0] = ev.bootstraps(); counts[1] = ev.batches(); }
         text = format_values(res);
     }) || emit(text, buf, cap, needed);
 }

@@ -36,10 +36,15 @@ class HbStats(C.Structure):
 GATE_DTYPE = np.dtype([("op", np.uint8), ("arity", np.uint8), ("flags", np.uint16), ("in", np.uint32, (4,)),
                        ("out", np.uint32), ("lut", np.uint64)], align=True)
 assert GATE_DTYPE.itemsize == C.sizeof(HbGate) == 32
+# hb_sop: one shortint block operation (LINEAR = 0 / LUT = 1), include/helm_b200.h
+SOP_LINEAR, SOP_LUT = 0, 1
+SOP_DTYPE = np.dtype([("kind", np.uint8), ("n_in", np.uint8), ("coef", np.int8, (4,)), ("cst", np.int16),
+                      ("in", np.uint32, (4,)), ("out", np.uint32), ("table", np.uint64)], align=True)
+assert SOP_DTYPE.itemsize == 40 and SOP_DTYPE.fields["in"][1] == 8 and SOP_DTYPE.fields["table"][1] == 32
 
 EXPORTS = ["hb_ctx_create", "hb_ctx_destroy", "hb_last_error", "hb_set_params", "hb_load_bsk", "hb_load_ksk",
            "hb_wires_create", "hb_wires_attach", "hb_wires_destroy", "hb_ct_words", "hb_wire_stride",
-           "hb_wires_device_ptr", "hb_wires_write", "hb_wires_read", "hb_wires_write_rows", "hb_wires_read_rows", "hb_wires_set_trivial", "hb_eval_level",
+           "hb_wires_device_ptr", "hb_wires_write", "hb_wires_read", "hb_wires_write_rows", "hb_wires_read_rows", "hb_wires_set_trivial", "hb_eval_level", "hb_eval_shortint_ops",
            "hb_sync", "hb_stats", "hb_stream", "hb_pbs_batch", "hb_keyswitch_batch", "hb_measure_fp64_peak"]
 
 _LIB = None
@@ -79,6 +84,7 @@ def lib():
         L.hb_wires_read_rows.argtypes = [vp, u32, u32, vp]
         L.hb_wires_set_trivial.argtypes = [vp, vp, u32, vp]
         L.hb_eval_level.argtypes = [vp, vp, vp, u32]
+        L.hb_eval_shortint_ops.argtypes = [vp, vp, vp, u32]
         L.hb_sync.argtypes = [vp]
         L.hb_stats.argtypes = [vp, C.POINTER(HbStats)]
         L.hb_stream.restype = vp
@@ -157,6 +163,10 @@ class Engine:
     def eval_level(self, wires, gates):
         gates = np.ascontiguousarray(gates, dtype=GATE_DTYPE)
         self._ck(self.L.hb_eval_level(self.h, wires.h, _ptr(gates), len(gates)), "hb_eval_level")
+
+    def eval_shortint_ops(self, wires, ops):
+        ops = np.ascontiguousarray(ops, dtype=SOP_DTYPE)
+        self._ck(self.L.hb_eval_shortint_ops(self.h, wires.h, _ptr(ops), len(ops)), "hb_eval_shortint_ops")
 
     def sync(self):
         self._ck(self.L.hb_sync(self.h), "hb_sync")

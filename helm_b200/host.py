@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libhelm_host.so")
 EXPORTS = ["hh_last_error", "hh_circuit_load", "hh_circuit_load_text", "hh_circuit_free", "hh_circuit_count",
            "hh_circuit_level_width", "hh_circuit_describe", "hh_circuit_eval_plain", "hh_read_input_csv",
-           "hh_session_create", "hh_session_free", "hh_session_run", "hh_session_stats"]
+           "hh_session_create", "hh_session_free", "hh_session_run", "hh_session_run_arith", "hh_session_stats"]
 _LIB = None
 
 
@@ -40,6 +40,8 @@ def lib():
         L.hh_session_create.argtypes = [cp, C.c_int, C.c_uint64, vp, vp, vp, sz, vp, sz, C.POINTER(vp)]
         L.hh_session_free.argtypes = [vp]
         L.hh_session_run.argtypes = [vp, vp, cp, C.c_int, C.c_int, C.c_int, vp, sz, C.POINTER(sz), C.POINTER(C.c_double)]
+        L.hh_session_run_arith.argtypes = [vp, vp, cp, cp, C.c_int, C.c_int, C.c_int, vp, sz, C.POINTER(sz),
+                                           C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
         L.hh_session_stats.argtypes = [vp, C.POINTER(C.c_uint64)]
         _LIB = L
     return _LIB
@@ -153,6 +155,14 @@ class Session:
         txt = _text(lambda b, c, n: self.L.hh_session_run(self.h, circuit.h, _fmt(inputs), cycles, int(all_wires),
                                                           int(verbose), b, c, n, secs))
         return _parse(txt), list(secs)
+
+    def run_arith(self, circuit, inputs=None, ptxt_type="u32", cycles=1, all_wires=False, verbose=False):
+        """Arithmetic mode (reference ArithCircuit).  Returns (values, seconds[3], {"bootstraps", "batches"})."""
+        secs = (C.c_double * 3)()
+        cnt = (C.c_uint64 * 2)()
+        txt = _text(lambda b, c, n: self.L.hh_session_run_arith(self.h, circuit.h, _fmt(inputs), ptxt_type.encode(), cycles,
+                                                                int(all_wires), int(verbose), b, c, n, secs, cnt))
+        return _parse(txt), list(secs), {"bootstraps": int(cnt[0]), "batches": int(cnt[1])}
 
     def stats(self):
         out = (C.c_uint64 * 4)()

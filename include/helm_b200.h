@@ -94,6 +94,25 @@ hb_status hb_wires_set_trivial(hb_wires*, const uint32_t* idx, uint32_t cnt, con
 /* evaluate every gate of one level as one batched launch sequence (asynchronous on the ctx stream).
  * No gate of the batch may read a wire written by another gate of the same batch. */
 hb_status hb_eval_level(hb_ctx*, hb_wires*, const hb_gate* gates, uint32_t n_gates);
+/* shortint block operations (order 1 parameter sets), the batched form of what tfhe-rs's integer layer issues block
+ * by block underneath FheUintN `+ - * << >>` (reached from reference src/gates.rs:306-702 through the high-level
+ * API): unchecked_add / unchecked_scalar_add / unchecked_sub (kind HB_SOP_LINEAR, no bootstrap) and
+ * apply_lookup_table / unchecked_apply_lookup_table_bivariate (kind HB_SOP_LUT: one keyswitch + one PBS).
+ * v = sum_s coef[s] * in[s] + cst (cst in message units, i.e. multiples of delta); LINEAR: out = v;
+ * LUT: out = encoding of table entry (v mod msg_mod*carry_mod), 4 bits per entry, entry i at bits [4i, 4i+4).
+ * Same batch rule as hb_eval_level: no op may read a wire another op of the batch writes (out == own input is fine
+ * for LINEAR). */
+enum { HB_SOP_LINEAR = 0, HB_SOP_LUT = 1 };
+typedef struct {
+    uint8_t kind;        /* HB_SOP_* */
+    uint8_t n_in;        /* 0..4 (0: LINEAR writes the trivial encryption of cst) */
+    int8_t coef[4];
+    int16_t cst;
+    uint32_t in[4];
+    uint32_t out;
+    uint64_t table;
+} hb_sop;
+hb_status hb_eval_shortint_ops(hb_ctx*, hb_wires*, const hb_sop* ops, uint32_t n_ops);
 hb_status hb_sync(hb_ctx*);
 hb_status hb_stats(hb_ctx*, hb_stats_t* out);
 /* CUDA stream of the context (cudaStream_t as void*), for callers that interleave collectives */

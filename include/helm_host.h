@@ -47,6 +47,11 @@ void hh_session_free(hh_session*);
  * wire with the plaintext evaluation).  seconds[3] = encrypt, evaluate, decrypt wall times (may be NULL). */
 int hh_session_run(hh_session*, const hh_circuit*, const char* inputs, int cycles, int all_wires, int verbose,
                    char* buf, size_t cap, size_t* needed, double* seconds);
+/* arithmetic mode (reference ArithCircuit, src/circuit.rs:1113-1483): ptxt_type "u8".."u128"; needs a session on a
+ * parameter set with msg_mod = carry_mod = 4 (shortint_m2c2 / toy64).  counts[2] = bootstraps, batches (may be NULL). */
+int hh_session_run_arith(hh_session*, const hh_circuit*, const char* inputs, const char* ptxt_type, int cycles,
+                         int all_wires, int verbose, char* buf, size_t cap, size_t* needed, double* seconds,
+                         uint64_t* counts);
 /* engine statistics of the session: pbs_count, ks_count, levels, kernel_launches */
 int hh_session_stats(hh_session*, uint64_t* out4);
 

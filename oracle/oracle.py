@@ -195,6 +195,11 @@ class Keys:
         v = ((self.phase(ct, 1) + d // 2) // d) % (2 * self.P.msg_mod * self.P.carry_mod)
         return v % self.P.msg_mod
 
+    def dec_shortint_full(self, ct):
+        """message and carry bits (mod msg_mod*carry_mod)"""
+        d = self.delta()
+        return ((self.phase(ct, 1) + d // 2) // d) % (self.P.msg_mod * self.P.carry_mod)
+
     def keyswitch(self, ct_big):
         ct_big = np.ascontiguousarray(ct_big, dtype=self.dtype)
         out = np.zeros(self.n + 1, dtype=self.dtype)

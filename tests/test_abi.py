@@ -31,6 +31,9 @@ def test_gate_struct_layout():
     assert C.sizeof(engine.HbGate) == 32 and engine.GATE_DTYPE.itemsize == 32
     assert engine.GATE_DTYPE.fields["out"][1] == 20 and engine.GATE_DTYPE.fields["lut"][1] == 24
     assert C.sizeof(engine.HbParams) == 44
+    # hb_sop { u8 kind, u8 n_in, i8 coef[4], i16 cst, u32 in[4], u32 out, u64 table }
+    assert engine.SOP_DTYPE.itemsize == 40 and engine.SOP_DTYPE.fields["cst"][1] == 6
+    assert engine.SOP_DTYPE.fields["out"][1] == 24 and engine.SOP_DTYPE.fields["table"][1] == 32
 
 
 def test_no_cpu_fallback():
