@@ -208,10 +208,10 @@ def main():
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from helm_b200 import shard
     W = args.width
-    assert W % world == 0
-    Wr = W // world
-    g0 = rank * Wr
+    assert W % world == 0, "the bench level width must divide by the number of GPUs"
+    g0, Wr = shard.level_slice(W, world, rank)
 
     K = O.Keys(PARAM_SET, seed=3)
     eng = helm_b200.Engine(K.params, device=local)
@@ -234,9 +234,8 @@ def main():
 
     def exchange(lvl):
         if world > 1:
-            blk = wt[lvl * W:(lvl + 1) * W]
             with torch.cuda.stream(ext):
-                dist.all_gather_into_tensor(blk, blk[g0:g0 + Wr])
+                shard.exchange_level(dist, wt[lvl * W:(lvl + 1) * W], world, rank)
 
     def step_resident(s):
         lvl = s % DEPTH + 1
@@ -357,7 +356,7 @@ def main():
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic", "config": workload_config(args, world),
-                "roofline": {"bound": "fp64", "kernel": "pbs_kernel<u32,N=512,k=2,l=3> (blind rotation)",
+                "roofline": {"bound": "fp64", "kernel": "pbs16_kernel<u32,K=2,L=3,BL=6,G=4> (blind rotation + sample extract)",
                              "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s",
                              "frac": (ach / fp64_peak) if ach else None, "traffic": None,
                              "peak_source": "measured in this run: register-resident DFMA loop (hb_measure_fp64_peak); "
