@@ -113,6 +113,11 @@ int hh_circuit_eval_plain(const hh_circuit* c, const char* inputs, const char* p
     }) || emit(s, buf, cap, needed);
 }
 
+int hh_preprocess_yosys(const char* yosys_text, char* buf, size_t cap, size_t* needed) {
+    std::string s;
+    return guarded([&] { s = preprocess_yosys_gates(yosys_text ? yosys_text : ""); }) || emit(s, buf, cap, needed);
+}
+
 int hh_read_input_csv(const char* path, const char* ptxt_type, char* buf, size_t cap, size_t* needed) {
     std::string s;
     return guarded([&] { s = format_values(read_input_wires(path, ptxt_type ? ptxt_type : "bool")); }) || emit(s, buf, cap, needed);

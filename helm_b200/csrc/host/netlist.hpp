@@ -63,5 +63,7 @@ Ptxt parse_input_wire(const std::string& text, const std::string& ptxt_type);   
 std::string hex_to_bitstring(const std::string& hex);                              // src/lib.rs:183-194
 void expand_bus_value(const std::string& wire, const std::string& hex, size_t width, WireValues* out);
 void write_output_wires(const std::string& file_name, const WireValues& values);
+// Yosys gate-cell netlist -> HELM netlist text (preprocess.cpp; reference hdl-benchmarks/src/lib.rs)
+std::string preprocess_yosys_gates(const std::string& yosys_text);
 
 }  // namespace helm

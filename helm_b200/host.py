@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libhelm_host.so")
 EXPORTS = ["hh_last_error", "hh_circuit_load", "hh_circuit_load_text", "hh_circuit_free", "hh_circuit_count",
-           "hh_circuit_level_width", "hh_circuit_describe", "hh_circuit_eval_plain", "hh_read_input_csv",
+           "hh_circuit_level_width", "hh_circuit_describe", "hh_circuit_eval_plain", "hh_read_input_csv", "hh_preprocess_yosys",
            "hh_session_create", "hh_session_free", "hh_session_run", "hh_session_run_arith", "hh_session_stats"]
 _LIB = None
 
@@ -37,6 +37,7 @@ def lib():
         L.hh_circuit_describe.argtypes = [vp, vp, sz, C.POINTER(sz)]
         L.hh_circuit_eval_plain.argtypes = [vp, cp, cp, C.c_int, vp, sz, C.POINTER(sz)]
         L.hh_read_input_csv.argtypes = [cp, cp, vp, sz, C.POINTER(sz)]
+        L.hh_preprocess_yosys.argtypes = [cp, vp, sz, C.POINTER(sz)]
         L.hh_session_create.argtypes = [cp, C.c_int, C.c_uint64, vp, vp, vp, sz, vp, sz, C.POINTER(vp)]
         L.hh_session_free.argtypes = [vp]
         L.hh_session_run.argtypes = [vp, vp, cp, C.c_int, C.c_int, C.c_int, vp, sz, C.POINTER(sz), C.POINTER(C.c_double)]
@@ -81,6 +82,12 @@ def _fmt(values):
                    for k, v in values.items()).encode()
 
 
+def preprocess_yosys(text):
+    """Yosys gate-cell netlist text -> HELM netlist text (reference hdl-benchmarks preprocessor)."""
+    L = lib()
+    return _text(lambda b, c, n: L.hh_preprocess_yosys(text.encode(), b, c, n))
+
+
 def read_input_wires(path, ptxt_type="bool"):
     L = lib()
     return _parse(_text(lambda b, c, n: L.hh_read_input_csv(path.encode(), ptxt_type.encode(), b, c, n)))
@@ -110,6 +117,12 @@ class Circuit:
 
     def level_widths(self):
         return [int(self.L.hh_circuit_level_width(self.h, i)) for i in range(self.count(self.LEVELS))]
+
+    def inputs(self):
+        """Wires read by some gate and driven by none (primary inputs actually used)."""
+        g = self.gates()
+        driven = {x[3] for x in g}
+        return sorted({w for x in g for w in x[4] if w not in driven})
 
     def gates(self):
         """[(level, type, name, out, [inputs])] in level order."""

@@ -33,6 +33,9 @@ int hh_circuit_describe(const hh_circuit*, char* buf, size_t cap, size_t* needed
  * cycles > 1 feeds the wire map back like the reference main loop.  Writes every wire with a value. */
 int hh_circuit_eval_plain(const hh_circuit*, const char* inputs, const char* ptxt_type, int cycles,
                           char* buf, size_t cap, size_t* needed);
+/* Yosys structural Verilog (gate cells) -> HELM netlist text: the hdl-benchmarks preprocessor for gate netlists
+ * (reference hdl-benchmarks/src/lib.rs:319-391, 608-810; how c880 / c7552 of BASELINE.json configs[1] are produced) */
+int hh_preprocess_yosys(const char* yosys_text, char* buf, size_t cap, size_t* needed);
 /* CSV helper (reference read_input_wires): file -> "wire=value\n" lines */
 int hh_read_input_csv(const char* path, const char* ptxt_type, char* buf, size_t cap, size_t* needed);
 

@@ -8,7 +8,7 @@ SRC = "/root/reference/hdl-benchmarks"
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 NETS = ["processed-netlists/" + f for f in ("s27.v", "2-bit-adder.v", "c17.v", "16-bit-mult-gates.v", "8-bit-adder-lut-2-1.v",
         "8-bit-adder-lut-3-1.v", "chi_squared_arith.v", "invalid.v", "gates.v", "c17_lut_2.v")] + \
-       ["netlists/c880.v", "netlists/c7552.v"]
+       ["netlists/c880.v", "netlists/c7552.v", "netlists/c17.v"]
 CASES = ["2-bit-adder.inputs.csv", "2-bit-adder.outputs.csv", "8-bit-adder.inputs.csv", "bool_array.input.csv",
          "16-bit-mult.inputs.csv"] + ["chi_squared_arith_%d.%s.csv" % (i, k) for i in range(1, 5) for k in ("inputs", "outputs")]
 for rel in NETS:

@@ -111,3 +111,24 @@ def test_numeric_wire_names_quirk():
     assert quirk.level_widths() == [2]
     with pytest.raises(H.HostError, match="never become ready"):
         C(text="module m(a, y);\n input a;\n output y;\n and g1(a, zz, y);\nendmodule\n")
+
+
+def test_yosys_preprocessor_matches_checked_in_c17():  # hdl-benchmarks/src/lib.rs:319-391, 608-810
+    txt = H.preprocess_yosys(open(os.path.join(os.path.dirname(NET), "yosys", "c17.v")).read())
+    mine = C(text=txt)
+    ref = C(os.path.join(NET, "c17.v"))                # produced by the reference's own preprocessor
+    strip = lambda s: s.strip("_")                     # the checked-in file predates keeping Yosys' underscores
+    a = sorted((g[1], strip(g[3]), tuple(strip(w) for w in g[4])) for g in mine.gates())
+    b = sorted((g[1], strip(g[3]), tuple(strip(w) for w in g[4])) for g in ref.gates())
+    assert a == b and mine.level_widths() == ref.level_widths()
+    bits = {"G1": True, "G2": False, "G3": True, "G4": True, "G5": False}
+    va, vb = mine.evaluate(bits), ref.evaluate(bits)
+    assert va["G16"] == vb["G16"] and va["G17"] == vb["G17"]
+
+
+@pytest.mark.parametrize("name,levels,maxw,pbs_gates,mux", [("c880", 26, 51, 262, 0), ("c7552", 31, 180, 902, 135)])
+def test_iscas85_shapes(name, levels, maxw, pbs_gates, mux):
+    c = C(text=H.preprocess_yosys(open(os.path.join(os.path.dirname(NET), "yosys", name + ".v")).read()))
+    assert c.count(C.LEVELS) == levels and max(c.level_widths()) == maxw and c.count(C.PBS_GATES) == pbs_gates
+    assert sum(1 for g in c.gates() if g[1] == "mux") == mux
+    c.evaluate()                                        # all-false inputs evaluate without missing wires
