@@ -259,12 +259,32 @@ hb_status upload_jobs(hb_ctx* c, const std::vector<PbsJob>& pj, const std::vecto
     return HB_OK;
 }
 
+// Narrow batches (fewer gates than the GPU has SMs x a few) are latency-bound: one bootstrap is n sequential CMUX steps,
+// so what matters is the time of ONE step of ONE CTA.  Those batches run pbs_kernel with few gates per CTA and every
+// transform of a gate on its own half-warp instead of the throughput mapping.
+struct SmallVariant { size_t (*smem)(int n); cudaError_t (*launch)(const PbsArgs&, cudaStream_t, size_t smem); };
+const SmallVariant g_small_bool[] = {
+    {&Inst<uint32_t, 512, 2, 3, 16, 16, 1, 288, 1>::smem, &Inst<uint32_t, 512, 2, 3, 16, 16, 1, 288, 1>::launch},
+    {&Inst<uint32_t, 512, 2, 3, 16, 16, 1, 160, 1>::smem, &Inst<uint32_t, 512, 2, 3, 16, 16, 1, 160, 1>::launch},
+    {&Inst<uint32_t, 512, 2, 3, 16, 16, 2, 288, 1>::smem, &Inst<uint32_t, 512, 2, 3, 16, 16, 2, 288, 1>::launch},
+    {&Inst<uint32_t, 512, 2, 3, 16, 16, 1, 512, 1>::smem, &Inst<uint32_t, 512, 2, 3, 16, 16, 1, 512, 1>::launch},
+};
+
 hb_status launch_pbs(hb_ctx* c, const void* in, uint32_t in_stride, void* out, uint32_t out_stride, const PbsJob* jobs, uint32_t n_jobs) {
     if (!n_jobs) return HB_OK;
     const Shape& sh = g_shapes[c->shape];
     PbsArgs a;
     a.in = in; a.in_stride = in_stride; a.out = out; a.out_stride = out_stride; a.jobs = jobs; a.n_jobs = n_jobs;
     a.bsk = (const double2*)c->bsk_f.p; a.wtab = (const double2*)c->wtab.p; a.n = c->p.n; a.base_log = c->p.pbs_base_log;
+    static const int small_sel = getenv("HB_PBS_SMALL") ? atoi(getenv("HB_PBS_SMALL")) : 1;      // 0 disables
+    static const int small_max = getenv("HB_PBS_SMALL_MAX") ? atoi(getenv("HB_PBS_SMALL_MAX")) : 3;
+    if (small_sel > 0 && small_sel <= 4 && sh.bits == 32 && sh.N == 512 && sh.K == 2 && sh.L == 3 &&
+        n_jobs <= (uint32_t)(small_max * c->sm_count)) {
+        const SmallVariant& v = g_small_bool[small_sel - 1];
+        CU(c, v.launch(a, c->stream, v.smem(c->p.n)));
+        c->stats.kernel_launches++; c->stats.pbs_count += n_jobs;
+        return HB_OK;
+    }
     const size_t smem = sh.smem(c->p.n);
     if (smem > 227 * 1024) return fail(c, HB_ERR_UNSUPPORTED, "PBS shared memory footprint exceeds 227 KB");
     CU(c, sh.launch(a, c->stream, smem));
@@ -277,10 +297,29 @@ hb_status launch_ks(hb_ctx* c, const void* in, uint32_t in_stride, void* out, ui
     KsArgs a;
     a.in = in; a.in_stride = in_stride; a.out = out; a.out_stride = out_stride; a.jobs = jobs; a.n_jobs = n_jobs;
     a.ksk = c->ksk.p; a.n = c->p.n; a.kN = c->p.k * c->p.N; a.base_log = c->p.ks_base_log; a.level = c->p.ks_level;
-    const unsigned grid = (n_jobs + KS_TB - 1) / KS_TB;
-    if (c->p.torus_bits == 32) ks_kernel<uint32_t><<<grid, KS_NT, 0, c->stream>>>(a);
-    else ks_kernel<uint64_t><<<grid, KS_NT, 0, c->stream>>>(a);
+    const unsigned tiles = (n_jobs + KS_TB - 1) / KS_TB;
+    // narrow batches: fewer tiles than SMs would leave each CTA streaming the whole key alone -- split the mask
+    // dimension over gridDim.y CTAs (partial sums added atomically; wrapping integer adds, so still bit-exact)
+    int split = 1;
+    if (tiles * 2 <= (unsigned)c->sm_count) {
+        split = (2 * c->sm_count) / (int)tiles;
+        const int max_split = a.kN / 16;
+        if (split > max_split) split = max_split;
+        if (split < 1) split = 1;
+    }
+    a.split = split;
+    const dim3 grid(tiles, split);
+    if (c->p.torus_bits == 32) {
+        if (split > 1) ks_init_rows<uint32_t><<<n_jobs < 1024 ? n_jobs : 1024, 256, 0, c->stream>>>(a);
+        if (split > 1) ks_kernel<uint32_t, true><<<grid, KS_NT, 0, c->stream>>>(a);
+        else ks_kernel<uint32_t, false><<<grid, KS_NT, 0, c->stream>>>(a);
+    } else {
+        if (split > 1) ks_init_rows<uint64_t><<<n_jobs < 1024 ? n_jobs : 1024, 256, 0, c->stream>>>(a);
+        if (split > 1) ks_kernel<uint64_t, true><<<grid, KS_NT, 0, c->stream>>>(a);
+        else ks_kernel<uint64_t, false><<<grid, KS_NT, 0, c->stream>>>(a);
+    }
     CU(c, cudaGetLastError());
+    if (split > 1) c->stats.kernel_launches++;
     c->stats.kernel_launches++; c->stats.ks_count += n_jobs;
     return HB_OK;
 }

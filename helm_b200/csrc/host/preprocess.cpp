@@ -12,7 +12,7 @@
 //     S ? A : B (src/gates.rs:189-194, :265) while Yosys means S ? B : A; parity is with the reference, so the order
 //     is kept;
 //   * `\$_DFF_P_` cells drop the clock port (lib.rs:791-806);
-//   * an input assigned straight to an output becomes a `buf` (lib.rs:868-885).
+//   * an input (or another output) assigned straight to an output becomes a `buf` (lib.rs:868-885).
 // LUT cells ($lut / assign ... >> {...}) and arithmetic assigns are NOT restated here.
 #include <algorithm>
 #include <cctype>
@@ -73,9 +73,12 @@ std::string preprocess_yosys_gates(const std::string& text) {
         if (eq == std::string::npos) continue;
         std::string lhs = pp_trim(l.substr(7, eq - 7)), rhs = pp_trim(l.substr(eq + 1));
         if (!rhs.empty() && rhs.back() == ';') rhs = pp_trim(rhs.substr(0, rhs.size() - 1));
-        if (out_set.count(lhs) && in_set.count(rhs)) direct.emplace_back(rhs, lhs);
-        else if (out_set.count(lhs)) subst[rhs] = lhs;                   // internal net drives an output port
-        else subst[lhs] = rhs;                                           // internal net is an alias of rhs
+        if (out_set.count(lhs) && (in_set.count(rhs) || out_set.count(rhs))) direct.emplace_back(rhs, lhs);   // port -> output: buf
+        else if (out_set.count(lhs)) {
+            auto it = subst.find(rhs);
+            if (it != subst.end() && out_set.count(it->second)) direct.emplace_back(it->second, lhs);   // second output of one net
+            else subst[rhs] = lhs;                                       // internal net drives an output port
+        } else subst[lhs] = rhs;                                         // internal net is an alias of rhs
     }
     auto resolve = [&](std::string w) {
         for (int guard = 0; guard < 64; ++guard) {

@@ -9,6 +9,7 @@
 // + 1/8; shortint bivariate: l*factor + r) is fused into the digit prologue.
 #pragma once
 #include <stdint.h>
+#include <type_traits>
 
 namespace hb {
 
@@ -26,6 +27,8 @@ struct KsArgs {
     const KsJob* jobs; uint32_t n_jobs;
     const void* ksk;                         // [kN][l][n+1]
     int32_t n, kN, base_log, level;
+    int32_t split;                           // > 1: gridDim.y CTAs share one tile, each takes kN/split mask words and adds
+                                             // its partial sum atomically into rows prepared by ks_init_rows (narrow batches)
 };
 
 constexpr int KS_TB = 16;      // gates per CTA
@@ -34,9 +37,9 @@ constexpr int KS_QC = 3;       // output columns per thread: (n+1) <= KS_NT*KS_Q
 constexpr int KS_IC = 128;     // input mask words per digit chunk
 constexpr int KS_MAXL = 8;
 
-template <class T> __global__ void __launch_bounds__(KS_NT) ks_kernel(const KsArgs A) {
+template <class T, bool SPLIT> __global__ void __launch_bounds__(KS_NT) ks_kernel(const KsArgs A) {
     constexpr int BITS = sizeof(T) * 8;
-    __shared__ __align__(16) int8_t dig[KS_IC * KS_MAXL * KS_TB];      // [ii][lev][g]
+    __shared__ __align__(16) int8_t dig[KS_IC * KS_MAXL * KS_TB];      // [ii*L + lev][g]
     __shared__ KsJob jobs[KS_TB];
     const int tid = threadIdx.x, n = A.n, kN = A.kN, L = A.level, BL = A.base_log;
     const int job0 = blockIdx.x * KS_TB;
@@ -57,12 +60,15 @@ template <class T> __global__ void __launch_bounds__(KS_NT) ks_kernel(const KsAr
 
     const int tot = BL * L;
     const T mask = (((T)1) << BL) - 1;
-    for (int i0 = 0; i0 < kN; i0 += KS_IC) {
-        // digits of this chunk for all TB gates (tfhe-rs SignedDecomposer, App. A.3)
+    const int split = SPLIT ? A.split : 1;
+    const int per = ((kN + split - 1) / split + 3) & ~3;
+    const int ibeg = blockIdx.y * per, ilim = min(kN, ibeg + per);
+    for (int i0 = ibeg; i0 < ilim; i0 += KS_IC) {
+        // digits of this chunk for all TB gates (tfhe-rs SignedDecomposer, App. A.3), stored [ii*L + l][g]
         for (int t = tid; t < KS_IC * KS_TB; t += KS_NT) {
             const int ii = t % KS_IC, g = t / KS_IC, i = i0 + ii;
             T v = 0;
-            if (i < kN && g < njob) {
+            if (i < ilim && g < njob) {
                 const KsJob& j = jobs[g];
 #pragma unroll
                 for (int s = 0; s < 4; ++s)
@@ -80,29 +86,30 @@ template <class T> __global__ void __launch_bounds__(KS_NT) ks_kernel(const KsAr
                 T carry = ((res - 1) | state) & res;
                 carry >>= (BL - 1);
                 state += carry;
-                dig[(ii * KS_MAXL + l) * KS_TB + g] = (int8_t)((int32_t)res - (int32_t)(carry << BL));
+                dig[(ii * L + l) * KS_TB + g] = (int8_t)((int32_t)res - (int32_t)(carry << BL));
             }
         }
         __syncthreads();
-        const int iend = min(KS_IC, kN - i0);
-        for (int ii = 0; ii < iend; ++ii) {
-            for (int l = 0; l < L; ++l) {
-                const T* row = ksk + ((size_t)(i0 + ii) * L + l) * (n + 1);
-                T kv[KS_QC];
+        // rows (i, l) of the key are contiguous: one flat loop, unrolled so several rows' loads are in flight
+        const int rend = min(KS_IC, ilim - i0) * L;
+        const T* rowp = ksk + (size_t)i0 * L * (n + 1);
+#pragma unroll(SPLIT ? 4 : 1)
+        for (int rr = 0; rr < rend; ++rr) {
+            const T* row = rowp + (size_t)rr * (n + 1);
+            T kv[KS_QC];
 #pragma unroll
-                for (int q = 0; q < KS_QC; ++q) {
-                    const int c = tid + q * KS_NT;
-                    kv[q] = c <= n ? __ldg(row + c) : (T)0;
-                }
-                const int4 dv = *reinterpret_cast<const int4*>(&dig[(ii * KS_MAXL + l) * KS_TB]);
-                const int words[4] = {dv.x, dv.y, dv.z, dv.w};
+            for (int q = 0; q < KS_QC; ++q) {
+                const int c = tid + q * KS_NT;
+                kv[q] = c <= n ? __ldg(row + c) : (T)0;
+            }
+            const int4 dv = *reinterpret_cast<const int4*>(&dig[rr * KS_TB]);
+            const int words[4] = {dv.x, dv.y, dv.z, dv.w};
 #pragma unroll
-                for (int g = 0; g < KS_TB; ++g) {
-                    const int d = (int)(int8_t)((words[g >> 2] >> (8 * (g & 3))) & 0xff);
-                    const T dT = (T)(int64_t)d;
+            for (int g = 0; g < KS_TB; ++g) {
+                const int d = (int)(int8_t)((words[g >> 2] >> (8 * (g & 3))) & 0xff);
+                const T dT = (T)(int64_t)d;
 #pragma unroll
-                    for (int q = 0; q < KS_QC; ++q) acc[g][q] += dT * kv[q];
-                }
+                for (int q = 0; q < KS_QC; ++q) acc[g][q] += dT * kv[q];
             }
         }
         __syncthreads();
@@ -116,16 +123,41 @@ template <class T> __global__ void __launch_bounds__(KS_NT) ks_kernel(const KsAr
             for (int q = 0; q < KS_QC; ++q) {
                 const int c = tid + q * KS_NT;
                 if (c <= n) {
-                    T v = 0;
-                    if (c == n) {
+                    T* o = out + (size_t)j.dst * A.out_stride + c;
+                    if (SPLIT) {                          // wrapping integer adds commute: the result is bit-identical
+                        using AT = typename std::conditional<sizeof(T) == 4, unsigned int, unsigned long long>::type;
+                        atomicAdd(reinterpret_cast<AT*>(o), (AT)(T)(0 - acc[g][q]));
+                    } else {
+                        T v = 0;
+                        if (c == n) {
 #pragma unroll
-                        for (int s = 0; s < 4; ++s)
-                            if (j.c[s]) v += (T)(int64_t)j.c[s] * in[(size_t)j.src[s] * A.in_stride + kN];
-                        v += (T)j.cst;
+                            for (int s = 0; s < 4; ++s)
+                                if (j.c[s]) v += (T)(int64_t)j.c[s] * in[(size_t)j.src[s] * A.in_stride + kN];
+                            v += (T)j.cst;
+                        }
+                        *o = v - acc[g][q];
                     }
-                    out[(size_t)j.dst * A.out_stride + c] = v - acc[g][q];
                 }
             }
+        }
+    }
+}
+
+// split mode, first pass: out row = (0, ..., 0, body of the fused linear combination)
+template <class T> __global__ void ks_init_rows(const KsArgs A) {
+    const T* in = reinterpret_cast<const T*>(A.in);
+    T* out = reinterpret_cast<T*>(A.out);
+    for (uint32_t r = blockIdx.x; r < A.n_jobs; r += gridDim.x) {
+        const KsJob j = A.jobs[r];
+        for (int c = threadIdx.x; c <= A.n; c += blockDim.x) {
+            T v = 0;
+            if (c == A.n) {
+#pragma unroll
+                for (int s = 0; s < 4; ++s)
+                    if (j.c[s]) v += (T)(int64_t)j.c[s] * in[(size_t)j.src[s] * A.in_stride + A.kN];
+                v += (T)j.cst;
+            }
+            out[(size_t)j.dst * A.out_stride + c] = v;
         }
     }
 }
