@@ -10,6 +10,9 @@
 #include "../../include/helm_b200.h"
 #include "pbs_kernel.cuh"
 #include "pbs16_kernel.cuh"
+#ifndef HB_TMEMW
+#define HB_TMEMW true
+#endif
 #include "ks_kernel.cuh"
 
 using namespace hb;
@@ -164,12 +167,12 @@ struct Inst {
 };
 
 // N = 512 shapes run the half-warp-per-polynomial kernel (pbs16_kernel.cuh); the key transform and the Fourier key layout are shared
-template <class T, int K, int L, int BL, int G, int MINB>
+template <class T, int K, int L, int BL, int G, int MINB, bool TMEMW>
 struct Inst16 {
     using C = Pbs16Cfg<T, K, L, G>;
     static size_t smem(int n) { return C::smem_bytes(n); }
     static cudaError_t launch(const PbsArgs& a, cudaStream_t s, size_t smem) {
-        auto kern = pbs16_kernel<T, K, L, BL, G, MINB>;
+        auto kern = pbs16_kernel<T, K, L, BL, G, MINB, TMEMW>;
         static bool attr_done = false;
         if (!attr_done) {
             cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
@@ -187,7 +190,7 @@ const Shape g_shapes[] = {
 #ifdef HB_PBS_V2
     Inst<uint32_t, 512, 2, 3, 16, 16, 2, 288, 2>::shape(),     // tfhe boolean DEFAULT_PARAMETERS
 #else
-    Inst16<uint32_t, 2, 3, 6, 4, 2>::shape(),                  // tfhe boolean DEFAULT_PARAMETERS
+    Inst16<uint32_t, 2, 3, 6, 4, 2, HB_TMEMW>::shape(),                  // tfhe boolean DEFAULT_PARAMETERS
 #endif
     Inst<uint32_t, 1024, 1, 3, 16, 32, 1, 192, 2>::shape(),    // concrete-core GPU path of the reference
     Inst<uint64_t, 512, 3, 1, 16, 16, 2, 128, 2>::shape(),     // PARAM_MESSAGE_1_CARRY_1_KS_PBS

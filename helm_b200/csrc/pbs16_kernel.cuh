@@ -40,6 +40,33 @@ __device__ __forceinline__ void mbar_wait(uint32_t addr, uint32_t parity) {
     } while (!ok);
 }
 
+// ---- tensor memory as per-thread scratch.  The kernel issues no MMA; TMEM (256 KB per SM, its own datapath) holds the
+// 2 x 16 inter-stage twiddles every thread needs in each forward / inverse transform, which otherwise are 15 % of the
+// shared-memory wavefronts (profiles/r01_v4_*).  Shape 32x32b: lane i of a warp reads/writes TMEM lane 32*(warp%4)+i,
+// consecutive 32-bit columns -- i.e. thread-private storage.
+__device__ __forceinline__ void tmem_alloc(uint32_t smem_dst, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tmem_st4(uint32_t taddr, double2 v) {      // one double2 = 4 columns
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(taddr),
+                 "r"(__double2loint(v.x)), "r"(__double2hiint(v.x)), "r"(__double2loint(v.y)), "r"(__double2hiint(v.y)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, double2 (&w)[4]) {  // four double2 = 16 columns
+    uint32_t r[16];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                 : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+        w[q] = make_double2(__hiloint2double((int)r[4 * q + 1], (int)r[4 * q]), __hiloint2double((int)r[4 * q + 3], (int)r[4 * q + 2]));
+}
+
 // Signed decomposition of a u32 torus value into L biased bytes (digit + 64), closed form of tfhe-rs
 // SignedDecomposer (App. A.3): with b = bit (BL-1) of the next residue, carry = (res + 2^(BL-1) - 1 + b) >> BL, hence
 // u = state + 2^(BL-1) - 1 + b gives digit = (u mod 2^BL) - (2^(BL-1) - 1) - b and next state = u >> BL.
@@ -74,7 +101,7 @@ struct Pbs16Cfg {
     }
 };
 
-template <class T, int K, int L, int BL, int G, int MINB>
+template <class T, int K, int L, int BL, int G, int MINB, bool TMEMW>
 __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const PbsArgs A) {
     using C = Pbs16Cfg<T, K, L, G>;
     constexpr int N = C::N, M = C::M, R = 16, NT = C::NT, XROW = C::XROW, AS = C::ASTRIDE, ROWS = (K + 1) * L;
@@ -94,6 +121,9 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
     const T* in = reinterpret_cast<const T*>(A.in);
     const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(atil) + (uint32_t)((((size_t)G * (n + 1) * 2 + 15) & ~(size_t)15));
     if (tid == 0) mbar_init(mbar, NT);
+    constexpr uint32_t TM_COLS = ((NT / 32 + 3) / 4) * 128;           // 2 x 64 columns per thread, warps sharing a lane quadrant side by side
+    static_assert(!TMEMW || (TM_COLS == 128 || TM_COLS == 256), "TMEM allocation must be a power of two");
+    if (TMEMW && tid < 32) tmem_alloc(mbar + 8, TM_COLS);
 
     for (int x = tid; x < M; x += NT) W[(x >> 4) * (R + 1) + (x & 15)] = A.wtab[x];
     // ---- prologue: linear combination + modulus switch (App. A.5)
@@ -148,6 +178,23 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
     const int j2 = HAS2 ? tid / REM1 : 0;
     const int s2 = (pos2 >> 4) * (R + 1) + (pos2 & 15);
     uint32_t parity = 0;
+    uint32_t tw_b = 0, tw_e = 0;                                      // TMEM addresses of this thread's W(idx, .) and W(., idx)
+    if constexpr (TMEMW) {
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        uint32_t tbase;
+        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tbase) : "r"(mbar + 8) : "memory");
+        const int warp = tid >> 5;
+        tw_b = tbase + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(warp >> 2) * 128u;
+        tw_e = tw_b + 64u;
+#pragma unroll
+        for (int q = 0; q < R; ++q) {
+            tmem_st4(tw_b + 4 * q, W[q * (R + 1) + idx]);
+            tmem_st4(tw_e + 4 * q, W[idx * (R + 1) + q]);
+        }
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    }
 
     for (int i = 0; i < n; ++i) {
         int any = 0;
@@ -214,8 +261,18 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
                 }
                 dft_regs<R, 1>(x);
                 double2 y[R];
+                if constexpr (TMEMW) {
 #pragma unroll
-                for (int k0 = 0; k0 < R; ++k0) y[k0] = cmul(x[brev<R>(k0)], W[k0 * (R + 1) + idx]);
+                    for (int q = 0; q < 4; ++q) {
+                        double2 w4[4];
+                        tmem_ld16(tw_b + 16 * q, w4);
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) y[4 * q + u] = cmul(x[brev<R>(4 * q + u)], w4[u]);
+                    }
+                } else {
+#pragma unroll
+                    for (int k0 = 0; k0 < R; ++k0) y[k0] = cmul(x[brev<R>(k0)], W[k0 * (R + 1) + idx]);
+                }
                 // ... then wait until every thread has consumed the previous level's spectra, and publish the row
                 if (lev > 0) { mbar_wait(mbar, parity); parity ^= 1u; }
 #pragma unroll
@@ -288,8 +345,18 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
 #pragma unroll
             for (int k1 = 0; k1 < R; ++k1) x[k1] = xc[k1];
             dft_regs<R, -1>(x);
+            if constexpr (TMEMW) {
 #pragma unroll
-            for (int j0 = 0; j0 < R; ++j0) xc[j0] = cmul_conj(x[brev<R>(j0)], W[idx * (R + 1) + j0]);
+                for (int q = 0; q < 4; ++q) {
+                    double2 w4[4];
+                    tmem_ld16(tw_e + 16 * q, w4);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) xc[4 * q + u] = cmul_conj(x[brev<R>(4 * q + u)], w4[u]);
+                }
+            } else {
+#pragma unroll
+                for (int j0 = 0; j0 < R; ++j0) xc[j0] = cmul_conj(x[brev<R>(j0)], W[idx * (R + 1) + j0]);
+            }
         }
         __syncwarp();
         // F: inverse radix-16 DFT over k0, untwist, round, wrapping add into the accumulator
@@ -325,6 +392,15 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
             o[x] = c == 0 ? ag[j * AS] : (T)(0 - ag[j * AS + N - c]);
         }
         if (tid == 0) o[K * N] = ag[K * AS];
+    }
+    if constexpr (TMEMW) {
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        if (tid < 32) {
+            uint32_t tbase;
+            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tbase) : "r"(mbar + 8) : "memory");
+            tmem_dealloc(tbase, TM_COLS);
+        }
     }
 }
 

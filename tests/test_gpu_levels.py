@@ -104,3 +104,31 @@ def test_shortint_lut_level(name, keys_factory, engine_factory, oracle_mod):
         # two valid samples of the PBS output noise (digit roundings differ), far inside the decoding margin
         assert d < K.delta() >> 6, "phase differs from the exact oracle by 2^%.1f" % np.log2(max(d, 1))
     w.close()
+
+
+def test_wide_level_throughput_kernel_bit_exact(keys_factory, engine_factory, oracle_mod):
+    """A level wider than the narrow-batch threshold (3 x SMs) runs the throughput kernel (pbs16_kernel: half-warp per
+    polynomial, TMEM-resident twiddles, split-barrier MAC); its ciphertexts must equal the oracle's exact-integer
+    back-end word for word, including the ragged last CTA (width not a multiple of 4 gates)."""
+    from helm_b200 import engine as E
+    K, eng = keys_factory("toy32"), engine_factory("toy32")
+    W = 601
+    rng = np.random.default_rng(17)
+    bits = rng.integers(0, 2, size=(W, 3))
+    ops = rng.choice([E.AND, E.NAND, E.OR, E.NOR, E.XOR, E.XNOR, E.MUX], size=W).astype(np.uint8)
+    w = eng.wires(4 * W)
+    cts = K.enc_bool_batch(bits.reshape(-1), 77000)
+    w.write_rows(0, cts)
+    ar = np.arange(W)
+    before = eng.stats()
+    eng.eval_level(w, E.make_gates(ops, 3 * ar, 3 * ar + 1, 3 * W + ar, in2=3 * ar + 2))
+    eng.sync()
+    assert eng.stats()["pbs_count"] - before["pbs_count"] == W + int((ops == E.MUX).sum())
+    got = np.zeros((W, eng.ct_words), dtype=eng.dtype)
+    w.read_rows(3 * W, got)
+    for g in range(W):
+        want = K.bool_gate(int(ops[g]), cts[3 * g], cts[3 * g + 1], cts[3 * g + 2], mode=oracle_mod.EXACT)
+        assert np.array_equal(got[g], want), "gate %d op %d differs" % (g, ops[g])
+        x, y, s = (int(v) for v in bits[g])
+        assert K.dec_bool(got[g]) == bool(_plain(E, int(ops[g]), x, y, s))
+    w.close()
