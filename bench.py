@@ -33,6 +33,7 @@ sys.path.insert(0, ROOT)
 W_DEFAULT, DEPTH = 65536, 32
 PARAM_SET = "boolean_default"
 F_CMUX = 196608.0            # flops per CMUX step, boolean default
+NCU_DRAM_BYTES_PER_LAUNCH = 12.094210e9 + 294.716928e6     # profiles/r01_v5_pbs16_kernel_ncu.txt
 GATE_OPS = 6                 # AND NAND OR NOR XOR XNOR
 
 
@@ -176,6 +177,29 @@ def hbm_peak_gbs():
         return 6650.0        # fallback stated in B200_PROFILING.md
 
 
+def iscas_latency(name, device):
+    """End-to-end latency of one ISCAS'85 netlist in gates mode (all-false inputs, the reference README invocation):
+    evaluate = every level as one hb_eval_level batch, wires resident; outputs checked against the plaintext netlist."""
+    from helm_b200 import host as H
+    path = os.path.join(ROOT, "tests", "golden", "yosys", name + ".v")
+    if not os.path.exists(path):
+        return None
+    circ = H.Circuit(text=H.preprocess_yosys(open(path).read()))
+    sess = H.Session(PARAM_SET, device=device, seed=5)
+    want = circ.evaluate()
+    best = None
+    for rep in range(3):
+        got, secs = sess.run(circ)
+        assert all(bool(got[k]) == bool(want[k]) for k in got), "c7552: decrypted outputs differ from the plaintext netlist"
+        best = secs if best is None or secs[1] < best[1] else best
+    widths = circ.level_widths()
+    pbs = circ.count(H.Circuit.PBS_GATES) + sum(1 for g in circ.gates() if g[1] == "mux")
+    sess.close()
+    return {"netlist": name, "levels": len(widths), "max_width": max(widths), "pbs": pbs,
+            "evaluate_ms": 1e3 * best[1], "encrypt_ms": 1e3 * best[0], "decrypt_ms": 1e3 * best[2],
+            "pbs_per_s": pbs / best[1], "inputs": "all false", "outputs_verified": True}
+
+
 # ---------------------------------------------------------------- GPU arm
 def main():
     ap = argparse.ArgumentParser()
@@ -187,6 +211,7 @@ def main():
     ap.add_argument("--cpu-gates", type=int, default=0, help="CPU sample size (gates); default 4 x host threads")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-latency", action="store_true", help="skip the c7552 gates-mode latency leg")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3
@@ -347,6 +372,12 @@ def main():
                "sample": "%d gates of level 1 (of %d), oracle f64-FFT mode, OpenMP one gate per thread; %.1f s; "
                          "decrypts identical to the GPU outputs: %s" % (sample, W, dt, same_bits)}
 
+    # ---- BASELINE.json metric, second half: c7552 gates-mode end-to-end latency (configs[1]) through the host library
+    # (Yosys netlist -> restated preprocessor -> levelizer -> one hb_eval_level per level), N = 1 only
+    c7552 = None
+    if rank == 0 and world == 1 and not args.no_latency:
+        c7552 = iscas_latency("c7552", local)
+
     if rank == 0:
         value = W * args.steps / (ms_total * 1e-3)
         flops_per_launch = Wr * K.n * F_CMUX
@@ -358,13 +389,17 @@ def main():
                 "data": "synthetic", "config": workload_config(args, world),
                 "roofline": {"bound": "fp64", "kernel": "pbs16_kernel<u32,K=2,L=3,BL=6,G=4> (blind rotation + sample extract)",
                              "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s",
-                             "frac": (ach / fp64_peak) if ach else None, "traffic": None,
+                             "frac": (ach / fp64_peak) if ach else None,
+                             "traffic": NCU_DRAM_BYTES_PER_LAUNCH if (world == 1 and W == W_DEFAULT) else None,
+                             "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one full-width launch, "
+                                               "profiles/r01_v5_pbs16_kernel_ncu.txt (the kernel is FP64-bound: the "
+                                               "Fourier key stays in L2, DRAM traffic is ~22 GB/s)",
                              "peak_source": "measured in this run: register-resident DFMA loop (hb_measure_fp64_peak); "
                                             "MEASURED_PEAKS.json has no FP64 entry",
                              "flops_per_launch": flops_per_launch, "kernel_ms": pbs_ms, "ks_kernel_ms": ks_ms,
                              "hbm_floor_ms": 1e3 * (bsk_bytes + 3.0 * Wr * words * 4) / (hbm_peak_gbs() * 1e9)},
                 "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
-                "verified": verified}
+                "verified": verified, "c7552_gates_mode": c7552}
         print(json.dumps(line))
     wires.close()
     eng.close()

@@ -2,7 +2,7 @@
 # usage: gpu_check.sh [bench args]   -- GPU parity tests, then a short bench run
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
-timeout 900 python bench.py --steps 4 --no-cpu "$@" > gpurun_out/bench_quick.json 2> gpurun_out/bench_quick.err; echo "bench rc=$?"; tail -3 gpurun_out/bench_quick.err
+timeout 900 python bench.py --steps 4 --no-cpu --no-latency "$@" > gpurun_out/bench_quick.json 2> gpurun_out/bench_quick.err; echo "bench rc=$?"; tail -3 gpurun_out/bench_quick.err
 python - <<'PY'
 import json
 try:
