@@ -13,6 +13,9 @@
 #ifndef HB_TMEMW
 #define HB_TMEMW true
 #endif
+#ifndef HB_PBS16_G
+#define HB_PBS16_G 4
+#endif
 #include "ks_kernel.cuh"
 
 using namespace hb;
@@ -57,6 +60,7 @@ struct hb_ctx {
     int shape = -1;                        // index into the kernel shape table
     DevBuf bsk_f, ksk, wtab;               // resident keys
     DevBuf scratch_a, scratch_b;           // PBS->KS (order 0) or KS->PBS (order 1) intermediates
+    DevBuf atil;                           // switched masks of the running PBS batch (pbs16_kernel)
     DevBuf jobs_dev, stage_dev, idx_dev;
     PinBuf jobs_pin, stage_pin;
     hb_stats_t stats{};
@@ -169,7 +173,7 @@ struct Inst {
 // N = 512 shapes run the half-warp-per-polynomial kernel (pbs16_kernel.cuh); the key transform and the Fourier key layout are shared
 template <class T, int K, int L, int BL, int G, int MINB, bool TMEMW>
 struct Inst16 {
-    using C = Pbs16Cfg<T, K, L, G>;
+    using C = Pbs16Cfg<T, K, L, G, TMEMW>;
     static size_t smem(int n) { return C::smem_bytes(n); }
     static cudaError_t launch(const PbsArgs& a, cudaStream_t s, size_t smem) {
         auto kern = pbs16_kernel<T, K, L, BL, G, MINB, TMEMW>;
@@ -190,7 +194,7 @@ const Shape g_shapes[] = {
 #ifdef HB_PBS_V2
     Inst<uint32_t, 512, 2, 3, 16, 16, 2, 288, 2>::shape(),     // tfhe boolean DEFAULT_PARAMETERS
 #else
-    Inst16<uint32_t, 2, 3, 6, 4, 2, HB_TMEMW>::shape(),                  // tfhe boolean DEFAULT_PARAMETERS
+    Inst16<uint32_t, 2, 3, 6, HB_PBS16_G, 8 / HB_PBS16_G, HB_TMEMW>::shape(),                  // tfhe boolean DEFAULT_PARAMETERS
 #endif
     Inst<uint32_t, 1024, 1, 3, 16, 32, 1, 192, 2>::shape(),    // concrete-core GPU path of the reference
     Inst<uint64_t, 512, 3, 1, 16, 16, 2, 128, 2>::shape(),     // PARAM_MESSAGE_1_CARRY_1_KS_PBS
@@ -276,7 +280,7 @@ const SmallVariant g_small_bool[] = {
 hb_status launch_pbs(hb_ctx* c, const void* in, uint32_t in_stride, void* out, uint32_t out_stride, const PbsJob* jobs, uint32_t n_jobs) {
     if (!n_jobs) return HB_OK;
     const Shape& sh = g_shapes[c->shape];
-    PbsArgs a;
+    PbsArgs a{};
     a.in = in; a.in_stride = in_stride; a.out = out; a.out_stride = out_stride; a.jobs = jobs; a.n_jobs = n_jobs;
     a.bsk = (const double2*)c->bsk_f.p; a.wtab = (const double2*)c->wtab.p; a.n = c->p.n; a.base_log = c->p.pbs_base_log;
     static const int small_sel = getenv("HB_PBS_SMALL") ? atoi(getenv("HB_PBS_SMALL")) : 1;      // 0 disables
@@ -290,6 +294,9 @@ hb_status launch_pbs(hb_ctx* c, const void* in, uint32_t in_stride, void* out, u
     }
     const size_t smem = sh.smem(c->p.n);
     if (smem > 227 * 1024) return fail(c, HB_ERR_UNSUPPORTED, "PBS shared memory footprint exceeds 227 KB");
+    a.atil_stride = (uint32_t)((c->p.n + 2 + 7) & ~7);
+    CU(c, c->atil.ensure(((size_t)n_jobs + 16) * a.atil_stride * sizeof(uint16_t)));
+    a.atil = (uint16_t*)c->atil.p;
     CU(c, sh.launch(a, c->stream, smem));
     c->stats.kernel_launches++; c->stats.pbs_count += n_jobs;
     return HB_OK;
@@ -382,7 +389,7 @@ hb_status hb_ctx_destroy(hb_ctx* c) {
     if (!c) return HB_ERR_ARG;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    for (DevBuf* b : {&c->bsk_f, &c->ksk, &c->wtab, &c->scratch_a, &c->scratch_b, &c->jobs_dev, &c->stage_dev, &c->idx_dev}) b->release();
+    for (DevBuf* b : {&c->bsk_f, &c->ksk, &c->wtab, &c->scratch_a, &c->scratch_b, &c->atil, &c->jobs_dev, &c->stage_dev, &c->idx_dev}) b->release();
     c->jobs_pin.release(); c->stage_pin.release();
     for (size_t i = 0; i < g_extra.size(); ++i)
         if (g_extra[i].first == c) {

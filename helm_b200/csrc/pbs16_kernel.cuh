@@ -85,51 +85,58 @@ template <int BL, int L> __device__ __forceinline__ void digit_bytes_u32(uint32_
     }
 }
 
-template <class T, int K, int L, int G>
+template <class T, int K, int L, int G, bool TMEMW>
 struct Pbs16Cfg {
     static constexpr int N = 512, M = 256, R = 16;
     static constexpr int NT = G * (K + 1) * R;
     static constexpr int XROW = R * (R + 1);               // one spectrum: [k0][j0], rows padded to 17 double2
     static constexpr bool EXT = sizeof(T) == 4;            // negacyclic-extended accumulator (2N words per polynomial)
     static constexpr int ASTRIDE = (EXT ? 2 * N : N) + 16;  // +16 words: odd polynomials land on the other 16 banks
-    static constexpr int REM = M > NT ? M - NT : 0;        // positions not covered by "one position per thread"
-    static_assert(NT >= M || REM * (K + 1) == NT, "MAC split needs NT >= M or (M - NT)(K+1) == NT");
+    // MAC work split: PP whole positions per thread (all gates, all outputs) + the REM left-over positions as
+    // (position, output) pairs, I2 per thread (all gates) -- every thread does the same number of complex FMAs
+    static constexpr int PP = NT >= M ? 1 : M / NT;
+    static constexpr int REM = NT >= M ? 0 : M - PP * NT;
+    static constexpr int I2 = REM * (K + 1) / NT;
+    static constexpr int NGRP = PP > I2 ? PP : I2;
+    static_assert(NT >= M ? NT == M : (REM * (K + 1)) % NT == 0, "MAC split must divide evenly");
     static_assert(NT % 32 == 0, "whole warps");
-    __host__ __device__ static constexpr size_t smem_bytes(int n) {
-        return (size_t)G * (K + 1) * XROW * sizeof(double2) + (size_t)XROW * sizeof(double2) +
-               (size_t)G * (K + 1) * ASTRIDE * sizeof(T) + (((size_t)G * (n + 1) * 2 + 15) & ~(size_t)15) + 16;
+    __host__ __device__ static constexpr size_t smem_bytes(int) {
+        return (size_t)G * (K + 1) * XROW * sizeof(double2) + (TMEMW ? 0 : (size_t)XROW * sizeof(double2)) +
+               (size_t)G * (K + 1) * ASTRIDE * sizeof(T) + 16;
     }
 };
 
 template <class T, int K, int L, int BL, int G, int MINB, bool TMEMW>
 __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const PbsArgs A) {
-    using C = Pbs16Cfg<T, K, L, G>;
+    using C = Pbs16Cfg<T, K, L, G, TMEMW>;
     constexpr int N = C::N, M = C::M, R = 16, NT = C::NT, XROW = C::XROW, AS = C::ASTRIDE, ROWS = (K + 1) * L;
     constexpr int TWA = HB_TW_DEN / (4 * R);
     constexpr bool EXT = C::EXT;
+    constexpr int PP = C::PP, REM = C::REM, I2 = C::I2, NGRP = C::NGRP;
     using Dig = DigPack<sizeof(T) == 4>;
     using DigT = typename Dig::type;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double2* X = reinterpret_cast<double2*>(smem_raw);                  // [G][K+1][XROW]
-    double2* W = X + (size_t)G * (K + 1) * XROW;                        // W(j0,k0) at k0*17+j0
-    T* acc = reinterpret_cast<T*>(W + XROW);                            // [G][K+1][AS]
-    uint16_t* atil = reinterpret_cast<uint16_t*>(acc + (size_t)G * (K + 1) * AS);   // [G][n+1]
+    double2* W = X + (size_t)G * (K + 1) * XROW;                        // W(j0,k0) at k0*17+j0 (only without TMEM)
+    T* acc = reinterpret_cast<T*>(W + (TMEMW ? 0 : XROW));              // [G][K+1][AS]
 
     const int tid = threadIdx.x;
     const int n = A.n;
     const int job0 = blockIdx.x * G;
     const T* in = reinterpret_cast<const T*>(A.in);
-    const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(atil) + (uint32_t)((((size_t)G * (n + 1) * 2 + 15) & ~(size_t)15));
+    const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(acc + (size_t)G * (K + 1) * AS);
     if (tid == 0) mbar_init(mbar, NT);
     constexpr uint32_t TM_COLS = ((NT / 32 + 3) / 4) * 128;           // 2 x 64 columns per thread, warps sharing a lane quadrant side by side
     static_assert(!TMEMW || (TM_COLS == 128 || TM_COLS == 256), "TMEM allocation must be a power of two");
     if (TMEMW && tid < 32) tmem_alloc(mbar + 8, TM_COLS);
 
-    for (int x = tid; x < M; x += NT) W[(x >> 4) * (R + 1) + (x & 15)] = A.wtab[x];
-    // ---- prologue: linear combination + modulus switch (App. A.5)
+    if (!TMEMW) for (int x = tid; x < M; x += NT) W[(x >> 4) * (R + 1) + (x & 15)] = A.wtab[x];
+    // ---- prologue: linear combination + modulus switch (App. A.5); the switched mask a~ goes to a global scratch row per
+    // job (read back one value per step through L1), the switched body b~ is used right away
     for (int g = 0; g < G; ++g) {
         const int jid = job0 + g;
-        if (jid >= (int)A.n_jobs) { for (int x = tid; x <= n; x += NT) atil[g * (n + 1) + x] = 0; continue; }
+        uint16_t* at = A.atil + (size_t)jid * A.atil_stride;            // rows exist for the padded job count
+        if (jid >= (int)A.n_jobs) { for (int x = tid; x <= n; x += NT) at[x] = 0; continue; }
         const PbsJob jb = A.jobs[jid];
         const T* s0 = in + (size_t)jb.src0 * A.in_stride;
         const T* s1 = in + (size_t)jb.src1 * A.in_stride;
@@ -139,17 +146,17 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
             if (jb.c1) v += (T)(int64_t)jb.c1 * s1[x];
             if (x == n) v += (T)jb.cst;
             const T sh = v >> (TorusOps<T>::BITS - ilog2c(N) - 2);
-            atil[g * (n + 1) + x] = (uint16_t)(((sh + 1) >> 1) & (2 * N - 1));
+            at[x] = (uint16_t)(((sh + 1) >> 1) & (2 * N - 1));
         }
     }
-    __syncthreads();
+    __syncthreads();                                                    // global writes of this CTA visible to this CTA
     // ---- accumulator = TV * X^{-b~}
     for (int g = 0; g < G; ++g) {
         const int jid = job0 + g;
         T* ag = acc + (size_t)g * (K + 1) * AS;
         if (jid >= (int)A.n_jobs) { for (int x = tid; x < (K + 1) * AS; x += NT) ag[x] = 0; continue; }
         const PbsJob jb = A.jobs[jid];
-        const int bt = atil[g * (n + 1) + n];
+        const int bt = A.atil[(size_t)jid * A.atil_stride + n];
         const int a0 = (2 * N - bt) & (2 * N - 1);
         for (int x = tid; x < K * AS; x += NT) ag[x] = 0;
         for (int c = tid; c < N; c += NT) {
@@ -167,16 +174,10 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
     const int g_own = gr / (K + 1);
     T* ap = acc + (size_t)gr * AS;            // this half-warp's accumulator polynomial
     double2* xr = X + (size_t)gr * XROW;      // and its spectrum buffer
-    // MAC roles: one position for every gate and every output polynomial, plus (when NT < M) one (position, output
-    // polynomial) pair of the remaining positions for every gate
-    const bool has1 = tid < M;
-    const int pos1 = tid < M ? tid : 0;
-    const int s1 = (pos1 >> 4) * (R + 1) + (pos1 & 15);
-    constexpr bool HAS2 = C::REM > 0;
-    constexpr int REM1 = HAS2 ? C::REM : 1;
-    const int pos2 = HAS2 ? NT + tid % REM1 : 0;
-    const int j2 = HAS2 ? tid / REM1 : 0;
-    const int s2 = (pos2 >> 4) * (R + 1) + (pos2 & 15);
+    const uint16_t* at_own = A.atil + (size_t)(job0 + g_own) * A.atil_stride;
+    // MAC roles: group q = whole position tid + q*NT (q < PP) and left-over item tid + q*NT (q < I2), an item being
+    // (position PP*NT + item % REM, output polynomial item / REM)
+    auto spos = [](int pos) { return (pos >> 4) * (R + 1) + (pos & 15); };
     uint32_t parity = 0;
     uint32_t tw_b = 0, tw_e = 0;                                      // TMEM addresses of this thread's W(idx, .) and W(., idx)
     if constexpr (TMEMW) {
@@ -189,24 +190,21 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
         tw_b = tbase + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(warp >> 2) * 128u;
         tw_e = tw_b + 64u;
 #pragma unroll
-        for (int q = 0; q < R; ++q) {
-            tmem_st4(tw_b + 4 * q, W[q * (R + 1) + idx]);
-            tmem_st4(tw_e + 4 * q, W[idx * (R + 1) + q]);
+        for (int q = 0; q < R; ++q) {                                   // wtab[k0*16 + j0] = W(j0, k0)
+            tmem_st4(tw_b + 4 * q, A.wtab[q * R + idx]);
+            tmem_st4(tw_e + 4 * q, A.wtab[idx * R + q]);
         }
         asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
     }
 
+    int a_next = at_own[0];
     for (int i = 0; i < n; ++i) {
-        int any = 0;
-#pragma unroll
-        for (int g = 0; g < G; ++g) any |= atil[g * (n + 1) + i];
-        if (any == 0) continue;                       // uniform across the CTA
-
+        const int a = a_next;
+        a_next = at_own[i + 1];                                         // index n is the body: harmless, never used as a mask
         // A: rotate-subtract and signed decomposition of this thread's 32 coefficients c = idx + 16 m, all L levels.
         // pk[lev][part] packs the digits of coefficients (c, c+M) for j1 = 2 part and 2 part + 1 (DigPack order).
         DigT pk[L][R / 2];
         {
-            const int a = atil[g_own * (n + 1) + i];
             if constexpr (EXT) {
                 const uint32_t b4 = (uint32_t)((idx - a) & (2 * N - 1)) << 2;     // byte offset of E[(idx - a) mod 2N]
                 const unsigned char* eb = reinterpret_cast<const unsigned char*>(ap);
@@ -239,13 +237,16 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
                 }
             }
         }
-        double2 o1[G][K + 1];
-        double2 o2[G];
+        double2 o1[PP][G][K + 1];
+        double2 o2[I2 > 0 ? I2 : 1][G];
 #pragma unroll
         for (int g = 0; g < G; ++g) {
-            o2[g] = make_double2(0.0, 0.0);
 #pragma unroll
-            for (int j = 0; j <= K; ++j) o1[g][j] = make_double2(0.0, 0.0);
+            for (int q = 0; q < (I2 > 0 ? I2 : 1); ++q) o2[q][g] = make_double2(0.0, 0.0);
+#pragma unroll
+            for (int q = 0; q < PP; ++q)
+#pragma unroll
+                for (int j = 0; j <= K; ++j) o1[q][g][j] = make_double2(0.0, 0.0);
         }
 
 #pragma unroll 1
@@ -289,34 +290,50 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
 #pragma unroll
                 for (int k1 = 0; k1 < R; ++k1) xc[k1] = x[brev<R>(k1)];
             }
-            // D: pointwise MAC of this level's (K+1) spectra per gate with rows lev*(K+1)+r of BSK_i.  The key loads do
-            // not depend on the spectra: issue them before the barrier.
+            // D: pointwise MAC of this level's (K+1) spectra per gate with rows lev*(K+1)+r of BSK_i, one group of
+            // (whole position, left-over item) at a time.  The key loads do not depend on the spectra: the first group's
+            // are issued before the barrier.
             const double2* bp = A.bsk + ((size_t)i * ROWS + lev * (K + 1)) * (K + 1) * M;
             double2 b1[K + 1][K + 1];
             double2 b2[K + 1];
+            auto load_group = [&](int q) {
+                if (q < PP) {
+                    const int pos = NT >= M ? tid : tid + q * NT;
 #pragma unroll
-            for (int r = 0; r <= K; ++r) {
+                    for (int r = 0; r <= K; ++r)
 #pragma unroll
-                for (int j = 0; j <= K; ++j) b1[r][j] = ldg_nc(bp + (size_t)(r * (K + 1) + j) * M + pos1);
-                if (HAS2) b2[r] = ldg_nc(bp + (size_t)(r * (K + 1) + j2) * M + pos2);
-            }
+                        for (int j = 0; j <= K; ++j) b1[r][j] = ldg_nc(bp + (size_t)(r * (K + 1) + j) * M + pos);
+                }
+                if (q < I2) {
+                    const int item = tid + q * NT, pos = PP * NT + item % (REM > 0 ? REM : 1), j2 = item / (REM > 0 ? REM : 1);
+#pragma unroll
+                    for (int r = 0; r <= K; ++r) b2[r] = ldg_nc(bp + (size_t)(r * (K + 1) + j2) * M + pos);
+                }
+            };
+            load_group(0);
             __syncthreads();
-            if (has1) {
 #pragma unroll
-                for (int r = 0; r <= K; ++r) {
+            for (int q = 0; q < NGRP; ++q) {
+                if (q > 0) load_group(q);
+                if (q < PP) {
+                    const int s1 = spos(NT >= M ? tid : tid + q * NT);
 #pragma unroll
-                    for (int g = 0; g < G; ++g) {
-                        const double2 f = X[((size_t)g * (K + 1) + r) * XROW + s1];
+                    for (int r = 0; r <= K; ++r) {
 #pragma unroll
-                        for (int j = 0; j <= K; ++j) cfma(o1[g][j], f, b1[r][j]);
+                        for (int g = 0; g < G; ++g) {
+                            const double2 f = X[((size_t)g * (K + 1) + r) * XROW + s1];
+#pragma unroll
+                            for (int j = 0; j <= K; ++j) cfma(o1[q][g][j], f, b1[r][j]);
+                        }
                     }
                 }
-            }
-            if (HAS2) {
+                if (q < I2) {
+                    const int item = tid + q * NT, s2 = spos(PP * NT + item % (REM > 0 ? REM : 1));
 #pragma unroll
-                for (int r = 0; r <= K; ++r) {
+                    for (int r = 0; r <= K; ++r) {
 #pragma unroll
-                    for (int g = 0; g < G; ++g) cfma(o2[g], X[((size_t)g * (K + 1) + r) * XROW + s2], b2[r]);
+                        for (int g = 0; g < G; ++g) cfma(o2[q][g], X[((size_t)g * (K + 1) + r) * XROW + s2], b2[r]);
+                    }
                 }
             }
             mbar_arrive(mbar);                       // this thread no longer reads this level's spectra
@@ -327,15 +344,19 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
         }
         // output spectra -> the buffers of the polynomials they belong to (once everyone is done reading them)
         mbar_wait(mbar, parity); parity ^= 1u;
-        if (has1) {
+#pragma unroll
+        for (int q = 0; q < PP; ++q) {
+            const int s1 = spos(NT >= M ? tid : tid + q * NT);
 #pragma unroll
             for (int g = 0; g < G; ++g)
 #pragma unroll
-                for (int j = 0; j <= K; ++j) X[((size_t)g * (K + 1) + j) * XROW + s1] = o1[g][j];
+                for (int j = 0; j <= K; ++j) X[((size_t)g * (K + 1) + j) * XROW + s1] = o1[q][g][j];
         }
-        if (HAS2) {
 #pragma unroll
-            for (int g = 0; g < G; ++g) X[((size_t)g * (K + 1) + j2) * XROW + s2] = o2[g];
+        for (int q = 0; q < I2; ++q) {
+            const int item = tid + q * NT, s2 = spos(PP * NT + item % (REM > 0 ? REM : 1)), j2 = item / (REM > 0 ? REM : 1);
+#pragma unroll
+            for (int g = 0; g < G; ++g) X[((size_t)g * (K + 1) + j2) * XROW + s2] = o2[q][g];
         }
         __syncthreads();
         // E: inverse radix-16 DFT over k1 of column k0 = idx, conj inter-stage twiddle

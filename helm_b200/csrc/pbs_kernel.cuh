@@ -40,6 +40,7 @@ struct PbsArgs {
     const double2* bsk;                      // [n][ROWS][K+1][M]
     const double2* wtab;                     // [2][M]: WA[k0*RB+j0], WB[j0*RA+k0]
     int32_t n;  int32_t base_log;
+    uint16_t* atil; uint32_t atil_stride;    // pbs16_kernel: switched masks, [jobs padded to the CTA tile][atil_stride]
 };
 
 template <class T> struct TorusOps;
