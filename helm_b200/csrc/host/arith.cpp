@@ -44,27 +44,50 @@ uint32_t RadixBuilder::tmp() {
 // Carry propagation.  state_i = 2 (block i generates a carry), 1 (propagates an incoming one), 0 (absorbs it);
 // an inclusive prefix scan with combine(prev, cur) = (cur == 1 ? prev : cur) gives for every block whether a carry
 // leaves it; result_i = (sum_i + carry_in_i) mod msg.
-void RadixBuilder::propagate(RadixProgram& p, size_t st, const std::vector<BlockExpr>& sums, uint32_t out) {
+size_t RadixBuilder::propagate(RadixProgram& p, size_t st, const std::vector<BlockExpr>& sums, uint32_t out, uint32_t* carry_out) {
     const int m = msg_;
     const uint64_t t_msg = table([m](int v) { return v % m; });
     const uint64_t t_state = table([m](int v) { return v >= m ? 2 : (v == m - 1 ? 1 : 0); });
     const uint64_t t_comb = table([m](int v) { const int prev = v / m, cur = v % m; return cur == 1 ? prev : cur; });
     const uint64_t t_fin = table([m](int v) { const int prev = v / m, ms = v % m; return (ms + (prev == 2)) % m; });
-    if (nb_ == 1) { p.lut(st, sums[0], t_msg, out); return; }
-    std::vector<uint32_t> msgr(nb_), state(nb_ - 1);
+    const uint64_t t_cout = table([](int v) { return v == 2 ? 1 : 0; });
+    const int ns = carry_out ? nb_ : nb_ - 1;                          // blocks whose outgoing carry is needed
+    if (ns == 0) { p.lut(st, sums[0], t_msg, out); return st + 1; }
+    std::vector<uint32_t> msgr(nb_), state(ns);
     p.lut(st, sums[0], t_msg, out);                                   // block 0 has no incoming carry
     for (int i = 1; i < nb_; ++i) { msgr[i] = tmp(); p.lut(st, sums[i], t_msg, msgr[i]); }
-    for (int i = 0; i + 1 < nb_; ++i) { state[i] = tmp(); p.lut(st, sums[i], t_state, state[i]); }
+    for (int i = 0; i < ns; ++i) { state[i] = tmp(); p.lut(st, sums[i], t_state, state[i]); }
     size_t s = st + 1;
-    for (int d = 1; d < nb_ - 1; d *= 2, ++s) {
+    for (int d = 1; d < ns; d *= 2, ++s) {
         std::vector<uint32_t> nxt(state);
-        for (int i = d; i + 1 < nb_; ++i) {
+        for (int i = d; i < ns; ++i) {
             nxt[i] = tmp();
             p.lut(s, BlockExpr::of(state[i]).plus(state[i - d], m), t_comb, nxt[i]);
         }
         state.swap(nxt);
     }
     for (int i = 1; i < nb_; ++i) p.lut(s, BlockExpr::of(msgr[i]).plus(state[i - 1], m), t_fin, out + i);
+    if (carry_out) { *carry_out = tmp(); p.lut(s, BlockExpr::of(state[nb_ - 1]), t_cout, *carry_out); }
+    return s + 1;
+}
+
+uint32_t RadixBuilder::zero_row(RadixProgram& p) {
+    if (zero_ == 0xffffffffu) { zero_ = tmp(); p.lin(0, BlockExpr::constant(0), zero_); }
+    return zero_;
+}
+
+size_t RadixBuilder::mux_rows(RadixProgram& p, size_t st, uint32_t sel, const std::vector<uint32_t>& a, const std::vector<uint32_t>& b,
+                              const std::vector<uint32_t>& out) {
+    const int m = msg_;
+    const uint64_t t_if = table([m](int v) { return (v / m) ? v % m : 0; });       // index = sel*msg + block
+    const uint64_t t_else = table([m](int v) { return (v / m) ? 0 : v % m; });
+    for (size_t j = 0; j < out.size(); ++j) {
+        const uint32_t t1 = tmp(), t2 = tmp();
+        p.lut(st, BlockExpr::of(a[j]).plus(sel, m), t_if, t1);
+        p.lut(st, BlockExpr::of(b[j]).plus(sel, m), t_else, t2);
+        p.lin(st + 1, BlockExpr::of(t1).plus(t2), out[j]);
+    }
+    return st + 2;
 }
 
 void RadixBuilder::add(RadixProgram& p, uint32_t a, uint32_t b, uint32_t out) {
@@ -195,6 +218,98 @@ void RadixBuilder::scalar_shift(RadixProgram& p, uint32_t a, unsigned k, bool le
     }
 }
 
+// Restoring division.  Per quotient bit (MSB first): R <- (R << 1) | next dividend bit; D <- R - b with carry-out c
+// (c = 1 iff R >= b); R <- c ? D : R; quotient bit = c.  With b = 0 every c is 1: the quotient is all ones (tfhe-rs).
+void RadixBuilder::div(RadixProgram& p, uint32_t a, uint32_t b, uint32_t out) {
+    const int m = msg_;
+    int bpb = 0; while ((1 << bpb) < m) ++bpb;                          // bits per block
+    const int bits = nb_ * bpb;
+    std::vector<uint32_t> R(nb_);
+    for (int j = 0; j < nb_; ++j) { R[j] = tmp(); p.lin(0, BlockExpr::constant(0), R[j]); }
+    for (int j = 0; j < nb_; ++j) p.lin(0, BlockExpr::constant(0), out + j);
+    size_t st = 1;
+    for (int i = bits - 1; i >= 0; --i) {
+        const int ab = i / bpb, sh = i % bpb;
+        // shift the remainder left by one bit, bringing in bit i of the dividend
+        std::vector<uint32_t> S(nb_);
+        const uint64_t t_in = table([m, sh](int v) { return (((v / m) << 1) % m) | (((v % m) >> sh) & 1); });   // R_0*m + a_blk
+        const uint64_t t_sh = table([m, bpb](int v) { return (((v / m) << 1) % m) | ((v % m) >> (bpb - 1)); }); // R_j*m + R_{j-1}
+        for (int j = 0; j < nb_; ++j) {
+            S[j] = tmp();
+            if (j == 0) p.lut(st, BlockExpr::of(a + ab).plus(R[0], m), t_in, S[0]);
+            else p.lut(st, BlockExpr::of(R[j - 1]).plus(R[j], m), t_sh, S[j]);
+        }
+        // D = S - b, c = carry out
+        std::vector<BlockExpr> sums;
+        for (int j = 0; j < nb_; ++j) {
+            BlockExpr e = BlockExpr::of(S[j]).plus(b + j, -1);
+            e.cst = m - 1 + (j == 0);
+            sums.push_back(e);
+        }
+        const uint32_t D = next_;
+        for (int j = 0; j < nb_; ++j) tmp();
+        uint32_t c = 0;
+        st = propagate(p, st + 1, sums, D, &c);
+        // R = c ? D : S ; quotient bit
+        std::vector<uint32_t> Dv(nb_), Rn(nb_);
+        for (int j = 0; j < nb_; ++j) { Dv[j] = D + (uint32_t)j; Rn[j] = tmp(); }
+        p.lin(st, BlockExpr::of(out + ab).plus(c, 1 << sh), out + ab);
+        st = mux_rows(p, st, c, Dv, S, Rn);
+        R.swap(Rn);
+    }
+}
+
+void RadixBuilder::scalar_div(RadixProgram& p, uint32_t a, unsigned __int128 k, uint32_t out) {
+    const uint32_t kb = next_;
+    for (int j = 0; j < nb_; ++j) { const uint32_t r = tmp(); p.lin(0, BlockExpr::constant((int)(k % msg_)), r); k /= msg_; }
+    RadixProgram q;                                                     // the divisor rows are written at stage 0; shift the division by one stage
+    div(q, a, kb, out);
+    for (size_t s = 0; s < q.stages.size(); ++s) {
+        if (p.stages.size() <= s + 1) p.stages.resize(s + 2);
+        p.stages[s + 1].insert(p.stages[s + 1].end(), q.stages[s].begin(), q.stages[s].end());
+    }
+}
+
+// Shift by an encrypted amount s (mod the bit width): for every bit t of s, cur <- s_t ? (cur shifted by 2^t) : cur.
+void RadixBuilder::shift(RadixProgram& p, uint32_t a, uint32_t amount, bool left, uint32_t out) {
+    const int m = msg_;
+    int bpb = 0; while ((1 << bpb) < m) ++bpb;
+    const int bits = nb_ * bpb;
+    int nsel = 0; while ((1 << nsel) < bits) ++nsel;
+    const uint32_t zero = zero_row(p);
+    std::vector<uint32_t> sel(nsel);
+    for (int t = 0; t < nsel; ++t) {
+        const int sh = t % bpb;
+        sel[t] = tmp();
+        p.lut(0, BlockExpr::of(amount + t / bpb), table([sh](int v) { return (v >> sh) & 1; }), sel[t]);
+    }
+    std::vector<uint32_t> cur(nb_);
+    for (int j = 0; j < nb_; ++j) cur[j] = a + (uint32_t)j;
+    size_t st = 1;
+    for (int t = 0; t < nsel; ++t) {
+        const int k = 1 << t, kb = k / bpb, s = k % bpb;
+        std::vector<uint32_t> sh_rows(nb_), nxt(nb_);
+        for (int i = 0; i < nb_; ++i) {
+            const int main = left ? i - kb : i + kb, nbr = left ? main - 1 : main + 1;
+            const bool has_main = main >= 0 && main < nb_, has_nbr = s != 0 && nbr >= 0 && nbr < nb_;
+            if (s == 0) { sh_rows[i] = has_main ? cur[main] : zero; continue; }
+            if (!has_main && !has_nbr) { sh_rows[i] = zero; continue; }
+            const uint64_t tb = left ? table([m, s, bpb](int v) { return (((v / m) << s) % m) | ((v % m) >> (bpb - s)); })
+                                     : table([m, s, bpb](int v) { return ((v / m) >> s) | (((v % m) << (bpb - s)) % m); });
+            BlockExpr e;
+            if (has_main) e.plus(cur[main], m);
+            if (has_nbr) e.plus(cur[nbr], 1);
+            sh_rows[i] = tmp();
+            p.lut(st, e, tb, sh_rows[i]);
+        }
+        if (s != 0) ++st;
+        const bool last = t + 1 == nsel;
+        for (int i = 0; i < nb_; ++i) nxt[i] = last ? out + (uint32_t)i : tmp();
+        st = mux_rows(p, st, sel[t], sh_rows, cur, nxt);
+        cur.swap(nxt);
+    }
+}
+
 // ---------------------------------------------------------------- ArithCircuit
 ArithCircuit::ArithCircuit(const ClientKey& ck, const ServerKey& sk, const Circuit& c, unsigned int_bits)
     : ck_(ck), sk_(sk), circuit_(c), bits_(int_bits) {
@@ -236,7 +351,8 @@ void ArithCircuit::build_gate(RadixBuilder& rb, RadixProgram& p, const EncWireMa
             case GateType::Mult: rb.scalar_mul(p, a, k, out); return;
             case GateType::Shl: rb.scalar_shift(p, a, (unsigned)(k % bits_), true, out); return;
             case GateType::Shr: rb.scalar_shift(p, a, (unsigned)(k % bits_), false, out); return;
-            default: throw Error("arithmetic mode: division is not offered by the B200 engine yet (cell " + g.name + ")");
+            case GateType::Div: rb.scalar_div(p, a, k, out); return;
+            default: throw Error("arithmetic cell " + g.name + ": unsupported type");
         }
     }
     const uint32_t a = base_row(enc, g.inputs[0]), b = base_row(enc, g.inputs[1]);
@@ -244,8 +360,10 @@ void ArithCircuit::build_gate(RadixBuilder& rb, RadixProgram& p, const EncWireMa
         case GateType::Add: rb.add(p, a, b, out); return;
         case GateType::Sub: rb.sub(p, a, b, out); return;
         case GateType::Mult: rb.mul(p, a, b, out); return;
-        case GateType::Div: throw Error("arithmetic mode: division is not offered by the B200 engine yet (cell " + g.name + ")");
-        default: throw Error("arithmetic mode: shifts by an encrypted amount are not offered by the B200 engine yet (cell " + g.name + ")");
+        case GateType::Div: rb.div(p, a, b, out); return;
+        case GateType::Shl: rb.shift(p, a, b, true, out); return;
+        case GateType::Shr: rb.shift(p, a, b, false, out); return;
+        default: throw Error("arithmetic cell " + g.name + ": unsupported type");
     }
 }
 
@@ -268,7 +386,10 @@ std::unique_ptr<EncWireMap> ArithCircuit::encrypt_inputs(const std::set<std::str
             uint32_t used = 0;
             for (const Gate& g : level) {
                 const int terms = nb_ * (nb_ + 1);                             // partial products of one multiplication
-                used += g.type == GateType::Mult ? (uint32_t)(4 * terms + 16 * nb_) : (uint32_t)(16 * nb_);
+                if (g.type == GateType::Mult) used += (uint32_t)(4 * terms + 16 * nb_);
+                else if (g.type == GateType::Div) used += (uint32_t)(2 * nb_) * (uint32_t)(16 * nb_) + (uint32_t)(4 * nb_);   // bits x (shift, subtract, select)
+                else if (g.type == GateType::Shl || g.type == GateType::Shr) used += (uint32_t)(64 * nb_);
+                else used += (uint32_t)(16 * nb_);
             }
             need = std::max(need, used);
         }

@@ -16,7 +16,8 @@
 //   mul by scalar          : the same compression over per-digit scaled copies (digit 1 costs nothing)
 //   shl / shr by scalar    : one bivariate LUT per block (block shift is a relabelling)
 //   copy                   : row copies
-// Not yet offered (Error): div and shifts by an encrypted amount.
+//   div                    : restoring long division (shift-in, subtract with carry-out, select), ct / ct and ct / scalar
+//   shl / shr by ciphertext: barrel shifter, one select per bit of the amount
 #pragma once
 #include "eval.hpp"
 
@@ -44,7 +45,7 @@ struct RadixProgram {
 class RadixBuilder {
 public:
     RadixBuilder(int msg_mod, int carry_mod, int blocks, uint32_t scratch_first, uint32_t scratch_rows);
-    void reset_scratch() { next_ = first_; }
+    void reset_scratch() { next_ = first_; zero_ = 0xffffffffu; }
     uint32_t scratch_used() const { return next_ - first_; }
     int blocks() const { return nb_; }
     // operands and results are `blocks` consecutive rows starting at the given row (little-endian blocks)
@@ -56,6 +57,11 @@ public:
     void scalar_mul(RadixProgram& p, uint32_t a, unsigned __int128 k, uint32_t out);
     void scalar_shift(RadixProgram& p, uint32_t a, unsigned k, bool left, uint32_t out);
     void copy(RadixProgram& p, uint32_t a, uint32_t out);
+    // restoring long division, one quotient bit per iteration (quotient of x / 0 is all ones, as tfhe-rs defines it)
+    void div(RadixProgram& p, uint32_t a, uint32_t b, uint32_t out);
+    void scalar_div(RadixProgram& p, uint32_t a, unsigned __int128 k, uint32_t out);
+    // shift by an encrypted amount (taken modulo the bit width): barrel shifter over the bits of the amount
+    void shift(RadixProgram& p, uint32_t a, uint32_t amount, bool left, uint32_t out);
     // table helpers: entry i = f(i) for i in [0, msg*carry)
     template <class F> uint64_t table(F f) const {
         uint64_t t = 0;
@@ -66,11 +72,18 @@ private:
     uint32_t tmp();
     // sums[i] < msg*carry with true value <= 2*msg - 1; writes the propagated result blocks to out..out+nb-1,
     // starting at stage `st`
-    void propagate(RadixProgram& p, size_t st, const std::vector<BlockExpr>& sums, uint32_t out);
+    // returns the first free stage; if carry_out != nullptr a clean 0/1 block with the carry out of the top block is
+    // produced as well (available at the returned stage)
+    size_t propagate(RadixProgram& p, size_t st, const std::vector<BlockExpr>& sums, uint32_t out, uint32_t* carry_out = nullptr);
+    // out_j = sel ? a_j : b_j for block row lists (sel: clean 0/1 block); two stages
+    size_t mux_rows(RadixProgram& p, size_t st, uint32_t sel, const std::vector<uint32_t>& a, const std::vector<uint32_t>& b,
+                    const std::vector<uint32_t>& out);
+    uint32_t zero_row(RadixProgram& p);
     // columns[k] = rows of clean blocks (value < msg) of weight msg^k; starts at stage `st`
     void compress(RadixProgram& p, size_t st, std::vector<std::vector<uint32_t>> columns, uint32_t out);
     int msg_, carry_, mc_, nb_;
     uint32_t first_, rows_, next_;
+    uint32_t zero_ = 0xffffffffu;
 };
 
 // ArithCircuit: tfhe high-level integers (FheUint8..128) -> radix blocks of a shortint parameter set with

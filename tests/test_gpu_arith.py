@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 NET = os.path.join(HERE, "golden", "netlists")
 CASES = os.path.join(HERE, "golden", "test-cases")
 
-CELLS = """module m (a, b, c, y0, y1, y2, y3, y4, y5, y6, y7, y8, y9, y10, y11, y12);
+CELLS = """module m (a, b, c, y0, y1, y2, y3, y4, y5, y6, y7, y8, y9, y10, y11, y12, y13, y14, y15, y16);
   input [7:0] a;
   input [7:0] b;
   input [7:0] c;
@@ -28,6 +28,10 @@ CELLS = """module m (a, b, c, y0, y1, y2, y3, y4, y5, y6, y7, y8, y9, y10, y11, 
   mult g10(y0, y1, y10);
   add g11(y10, y2, y11);
   mult g12(a, a, y12);
+  div g13(a, b, y13);
+  div g14(c, 7, y14);
+  shl g15(a, c, y15);
+  shr g16(b, c, y16);
 endmodule
 """
 
@@ -50,6 +54,8 @@ def test_every_cell_type_matches_plain_arithmetic(toy_session, ptxt_type):
         ins = {k: int(rng.integers(0, 1 << bits)) for k in "abc"}
         if trial == 0:
             ins = {"a": (1 << bits) - 1, "b": (1 << bits) - 1, "c": 0}          # every carry chain at full length
+        if trial == 1:
+            ins["b"] = 0                                                        # division by zero: all ones (tfhe-rs)
         want = c.evaluate(ins, ptxt_type)
         got, secs, cnt = toy_session.run_arith(c, ins, ptxt_type, all_wires=True)
         for w in want:
