@@ -132,7 +132,7 @@ def run_reference(args):
     W = args.width
     bits0 = (splitmix64(2, W) & np.uint64(1)).astype(np.uint8)
     threads = os.cpu_count() or 1
-    sample = max(threads, min(W, args.cpu_gates if args.cpu_gates else 4 * threads))
+    sample = max(threads, min(W, args.cpu_gates if args.cpu_gates else 64 * threads))       # ~2-3 s of host work per step
     # only the wires the sample reads need to exist: encrypt level 0 lazily
     times = []
     for s in range(args.warmup + args.steps):
@@ -220,7 +220,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--width", type=int, default=W_DEFAULT, help="gates per level (default: the BASELINE config, 65536)")
-    ap.add_argument("--cpu-gates", type=int, default=0, help="CPU sample size (gates); default 4 x host threads")
+    ap.add_argument("--cpu-gates", type=int, default=0, help="CPU sample size (gates); default 384 x host threads (cpu_baseline), 64 x per step (--impl reference)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-latency", action="store_true", help="skip the c7552 gates-mode latency leg")
@@ -374,7 +374,7 @@ def main():
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
-        sample = args.cpu_gates if args.cpu_gates else 4 * threads
+        sample = min(W, args.cpu_gates if args.cpu_gates else 384 * threads)                    # ~15 s of host work
         ops1, i0, i1 = synth_level(1, W)
         need = np.unique(np.concatenate([i0[:sample], i1[:sample]]))
         remap = np.zeros(W, dtype=np.uint32); remap[need] = np.arange(len(need), dtype=np.uint32)
