@@ -179,6 +179,8 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
     using Dig = typename C::Dig;
     using DigT = typename Dig::type;
     constexpr int PARTS = C::PARTS;
+    constexpr bool CHAIN_F = RA == RB && RA <= 32 && G * ROWS * RB <= NT;
+    constexpr bool CHAIN_I = RA == RB && RA <= 32 && G * (K + 1) * RA <= NT;
     DigT* digs = reinterpret_cast<DigT*>(acc + (size_t)G * (K + 1) * N);           // [G][ROWS][PARTS][RB]
     uint16_t* atil = reinterpret_cast<uint16_t*>(digs + (size_t)G * ROWS * PARTS * RB);   // [G][n+1]
 
@@ -263,7 +265,9 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
 #pragma unroll
             for (int k0 = 0; k0 < RA; ++k0) xr[k0 * (RB + 1) + j0] = cmul(x[brev<RA>(k0)], WA[k0 * RB + j0]);
         }
-        __syncthreads();
+        // the two stages of one row run on the same RA == RB consecutive threads when a single round covers every row:
+        // then the transpose only needs a warp-level sync (RA, RB <= 32 divide the warp)
+        if (CHAIN_F) __syncwarp(); else __syncthreads();
         // P2: radix-RB DFT over j0 (column k0), in place
         for (int t = tid; t < G * ROWS * RA; t += NT) {
             const int k0 = t % RA, grow = t / RA;
@@ -275,8 +279,19 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
 #pragma unroll
             for (int k1 = 0; k1 < RB; ++k1) xc[k1] = x[brev<RB>(k1)];
         }
+        // P3: pointwise MAC with BSK_i; one read of BSK feeds all G gates.  When every position has its own thread the
+        // first rows' key loads are issued before the barrier (they do not depend on the spectra)
+        constexpr bool PRE = M <= NT;
+        constexpr int NPRE = ROWS < 3 ? ROWS : 3;
+        double2 bpre[NPRE][K + 1];
+        if (PRE && tid < M) {
+            const double2* bp0 = A.bsk + (size_t)i * ROWS * (K + 1) * M + tid;
+#pragma unroll
+            for (int row = 0; row < NPRE; ++row)
+#pragma unroll
+                for (int j = 0; j <= K; ++j) bpre[row][j] = __ldg(bp0 + (size_t)(row * (K + 1) + j) * M);
+        }
         __syncthreads();
-        // P3: pointwise MAC with BSK_i; one read of BSK feeds all G gates
         for (int pos = tid; pos < M; pos += NT) {
             const int s = (pos / RB) * (RB + 1) + (pos % RB);
             double2 o[G][K + 1];
@@ -289,7 +304,7 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
             for (int row = 0; row < ROWS; ++row) {
                 double2 b[K + 1];
 #pragma unroll
-                for (int j = 0; j <= K; ++j) b[j] = __ldg(bp + (size_t)(row * (K + 1) + j) * M);
+                for (int j = 0; j <= K; ++j) b[j] = (PRE && row < NPRE) ? bpre[row][j] : __ldg(bp + (size_t)(row * (K + 1) + j) * M);
 #pragma unroll
                 for (int g = 0; g < G; ++g) {
                     const double2 f = X[((size_t)g * ROWS + row) * XROW + s];
@@ -314,7 +329,7 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
 #pragma unroll
             for (int j0 = 0; j0 < RB; ++j0) xc[j0] = cmul_conj(x[brev<RB>(j0)], WB[j0 * RA + k0]);
         }
-        __syncthreads();
+        if (CHAIN_I) __syncwarp(); else __syncthreads();
         // P5: inverse radix-RA DFT over k0, untwist, round, wrapping add into the accumulator
         for (int t = tid; t < G * (K + 1) * RB; t += NT) {
             const int j0 = t % RB, j = (t / RB) % (K + 1), g = t / (RB * (K + 1));
