@@ -144,7 +144,11 @@ struct Shape {
     cudaError_t (*launch)(const PbsArgs&, cudaStream_t, size_t smem);
     cudaError_t (*bsk_fft)(const void* std_bsk, double2* out, const double2* wtab, size_t polys, cudaStream_t);
     int BL = 0;                            // compile-time pbs_base_log of the instance (0: run-time)
+    // narrow batches (<= 3 x SMs bootstraps): one gate per CTA, every transform on its own group of threads
+    size_t (*small_smem)(int n) = nullptr;
+    cudaError_t (*small_launch)(const PbsArgs&, cudaStream_t, size_t smem) = nullptr;
 };
+template <class Small> constexpr Shape with_small(Shape s) { s.small_smem = &Small::smem; s.small_launch = &Small::launch; return s; }
 
 template <class T, int N, int K, int L, int RA, int RB, int G, int NT, int MINB>
 struct Inst {
@@ -191,14 +195,13 @@ struct Inst16 {
 };
 
 const Shape g_shapes[] = {
-#ifdef HB_PBS_V2
-    Inst<uint32_t, 512, 2, 3, 16, 16, 2, 288, 2>::shape(),     // tfhe boolean DEFAULT_PARAMETERS
-#else
-    Inst16<uint32_t, 2, 3, 6, HB_PBS16_G, 8 / HB_PBS16_G, HB_TMEMW>::shape(),                  // tfhe boolean DEFAULT_PARAMETERS
-#endif
+    // tfhe boolean DEFAULT_PARAMETERS
+    with_small<Inst<uint32_t, 512, 2, 3, 16, 16, 1, 288, 1>>(Inst16<uint32_t, 2, 3, 6, HB_PBS16_G, 8 / HB_PBS16_G, HB_TMEMW>::shape()),
     Inst<uint32_t, 1024, 1, 3, 16, 32, 1, 192, 2>::shape(),    // concrete-core GPU path of the reference
-    Inst<uint64_t, 512, 3, 1, 16, 16, 2, 128, 2>::shape(),     // PARAM_MESSAGE_1_CARRY_1_KS_PBS
-    Inst<uint64_t, 2048, 1, 1, 32, 32, 2, 128, 1>::shape(),    // PARAM_MESSAGE_2_CARRY_2_KS_PBS
+    // PARAM_MESSAGE_1_CARRY_1_KS_PBS / PARAM_MESSAGE_2_CARRY_1_KS_PBS
+    with_small<Inst<uint64_t, 512, 3, 1, 16, 16, 1, 256, 1>>(Inst<uint64_t, 512, 3, 1, 16, 16, 2, 128, 2>::shape()),
+    // PARAM_MESSAGE_2_CARRY_2_KS_PBS
+    with_small<Inst<uint64_t, 2048, 1, 1, 32, 32, 1, 256, 1>>(Inst<uint64_t, 2048, 1, 1, 32, 32, 2, 128, 1>::shape()),
 };
 
 int find_shape(const hb_params& p) {
@@ -266,31 +269,23 @@ hb_status upload_jobs(hb_ctx* c, const std::vector<PbsJob>& pj, const std::vecto
     return HB_OK;
 }
 
-// Narrow batches (fewer gates than the GPU has SMs x a few) are latency-bound: one bootstrap is n sequential CMUX steps,
-// so what matters is the time of ONE step of ONE CTA.  Those batches run pbs_kernel with few gates per CTA and every
-// transform of a gate on its own half-warp instead of the throughput mapping.
-struct SmallVariant { size_t (*smem)(int n); cudaError_t (*launch)(const PbsArgs&, cudaStream_t, size_t smem); };
-const SmallVariant g_small_bool[] = {
-    {&Inst<uint32_t, 512, 2, 3, 16, 16, 1, 288, 1>::smem, &Inst<uint32_t, 512, 2, 3, 16, 16, 1, 288, 1>::launch},
-    {&Inst<uint32_t, 512, 2, 3, 16, 16, 1, 160, 1>::smem, &Inst<uint32_t, 512, 2, 3, 16, 16, 1, 160, 1>::launch},
-    {&Inst<uint32_t, 512, 2, 3, 16, 16, 2, 288, 1>::smem, &Inst<uint32_t, 512, 2, 3, 16, 16, 2, 288, 1>::launch},
-    {&Inst<uint32_t, 512, 2, 3, 16, 16, 1, 512, 1>::smem, &Inst<uint32_t, 512, 2, 3, 16, 16, 1, 512, 1>::launch},
-};
-
 hb_status launch_pbs(hb_ctx* c, const void* in, uint32_t in_stride, void* out, uint32_t out_stride, const PbsJob* jobs, uint32_t n_jobs) {
     if (!n_jobs) return HB_OK;
     const Shape& sh = g_shapes[c->shape];
     PbsArgs a{};
     a.in = in; a.in_stride = in_stride; a.out = out; a.out_stride = out_stride; a.jobs = jobs; a.n_jobs = n_jobs;
     a.bsk = (const double2*)c->bsk_f.p; a.wtab = (const double2*)c->wtab.p; a.n = c->p.n; a.base_log = c->p.pbs_base_log;
-    static const int small_sel = getenv("HB_PBS_SMALL") ? atoi(getenv("HB_PBS_SMALL")) : 1;      // 0 disables
+    // Narrow batches are latency-bound (one bootstrap is n sequential CMUX steps, so what matters is the time of ONE step of
+    // ONE CTA): below small_max x SMs bootstraps they run the one-gate-per-CTA instance.  HB_PBS_SMALL=0 disables.
+    static const int small_on = getenv("HB_PBS_SMALL") ? atoi(getenv("HB_PBS_SMALL")) : 1;
     static const int small_max = getenv("HB_PBS_SMALL_MAX") ? atoi(getenv("HB_PBS_SMALL_MAX")) : 3;
-    if (small_sel > 0 && small_sel <= 4 && sh.bits == 32 && sh.N == 512 && sh.K == 2 && sh.L == 3 &&
-        n_jobs <= (uint32_t)(small_max * c->sm_count)) {
-        const SmallVariant& v = g_small_bool[small_sel - 1];
-        CU(c, v.launch(a, c->stream, v.smem(c->p.n)));
-        c->stats.kernel_launches++; c->stats.pbs_count += n_jobs;
-        return HB_OK;
+    if (small_on && sh.small_launch && n_jobs <= (uint32_t)(small_max * c->sm_count)) {
+        const size_t sm = sh.small_smem(c->p.n);
+        if (sm <= 227 * 1024) {
+            CU(c, sh.small_launch(a, c->stream, sm));
+            c->stats.kernel_launches++; c->stats.pbs_count += n_jobs;
+            return HB_OK;
+        }
     }
     const size_t smem = sh.smem(c->p.n);
     if (smem > 227 * 1024) return fail(c, HB_ERR_UNSUPPORTED, "PBS shared memory footprint exceeds 227 KB");
