@@ -314,6 +314,7 @@ def main():
     launches = int(st1["kernel_launches"] - st0["kernel_launches"])
     pbs_ms = (st1["pbs_ms_total"] - st0["pbs_ms_total"]) / args.steps
     ks_ms = (st1["ks_ms_total"] - st0["ks_ms_total"]) / args.steps
+    gap_ms = (st1["gap_ms_total"] - st0["gap_ms_total"]) / args.steps
 
     # ---- correctness of what was just timed: replay the netlist in plaintext and decrypt a sample of the last level
     nsteps = args.warmup + args.steps
@@ -413,7 +414,7 @@ def main():
                                                "Fourier key stays in L2, DRAM traffic is ~22 GB/s)",
                              "peak_source": "measured in this run: register-resident DFMA loop (hb_measure_fp64_peak); "
                                             "MEASURED_PEAKS.json has no FP64 entry",
-                             "flops_per_launch": flops_per_launch, "kernel_ms": pbs_ms, "ks_kernel_ms": ks_ms,
+                             "flops_per_launch": flops_per_launch, "kernel_ms": pbs_ms, "ks_kernel_ms": ks_ms, "gap_ms": gap_ms,
                              "hbm_floor_ms": 1e3 * (bsk_bytes + 3.0 * Wr * words * 4) / (hbm_peak_gbs() * 1e9)},
                 "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
                 "verified": verified, "c7552_gates_mode": c7552}

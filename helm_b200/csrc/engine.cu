@@ -229,10 +229,14 @@ std::vector<std::pair<hb_ctx*, CtxExtra*>> g_extra;
 CtxExtra* extra_of(hb_ctx* c) { for (auto& e : g_extra) if (e.first == c) return e.second; return nullptr; }
 
 // folds a finished slot's phase timings into the context totals (slot->done must have completed)
-void fold_timing(hb_ctx* c, JobSlot& s) {
+void fold_timing(hb_ctx* c, JobSlot& s, JobSlot* next = nullptr) {
     if (!s.pending) return;
     s.pending = false;
-    float a = 0, b = 0;
+    float a = 0, b = 0, g = 0;
+    // stream time between the end of this batch's kernels and the start of the next batch's (job upload, launch gaps)
+    if (next && next != &s && next->pending && cudaEventQuery(next->t[0]) == cudaSuccess &&
+        cudaEventElapsedTime(&g, s.t[2], next->t[0]) == cudaSuccess && g > 0) c->stats.gap_ms_total += g;
+    else (void)cudaGetLastError();
     if (cudaEventElapsedTime(&a, s.t[0], s.t[1]) != cudaSuccess || cudaEventElapsedTime(&b, s.t[1], s.t[2]) != cudaSuccess) return;
     const double pbs = s.first_is_pbs ? a : b, ks = s.first_is_pbs ? b : a;
     c->stats.pbs_ms = pbs; c->stats.ks_ms = ks;
@@ -252,7 +256,7 @@ hb_status upload_jobs(hb_ctx* c, const std::vector<PbsJob>& pj, const std::vecto
     CtxExtra* ex = extra_of(c);
     JobSlot& s = ex->slots[ex->next++ % NSLOT];
     CU(c, cudaEventSynchronize(s.done));
-    fold_timing(c, s);
+    fold_timing(c, s, &ex->slots[ex->next % NSLOT]);
     const size_t a = pj.size() * sizeof(PbsJob), b = kj.size() * sizeof(KsJob), d = lj.size() * sizeof(LinJob);
     const size_t oa = 0, ob = (a + 15) & ~(size_t)15, od = ob + ((b + 15) & ~(size_t)15), tot = od + d + 16;
     CU(c, s.pin.ensure(tot));
@@ -599,7 +603,7 @@ hb_status hb_stats(hb_ctx* c, hb_stats_t* out) {
         JobSlot& s = ex->slots[(ex->next + q) % NSLOT];
         if (!s.pending) continue;
         CU(c, cudaEventSynchronize(s.done));
-        fold_timing(c, s);
+        fold_timing(c, s, q + 1 < NSLOT ? &ex->slots[(ex->next + q + 1) % NSLOT] : nullptr);
     }
     *out = c->stats;
     return HB_OK;

@@ -118,6 +118,16 @@ int hh_preprocess_yosys(const char* yosys_text, char* buf, size_t cap, size_t* n
     return guarded([&] { s = preprocess_yosys_gates(yosys_text ? yosys_text : ""); }) || emit(s, buf, cap, needed);
 }
 
+int hh_preprocess_yosys_mode(const char* yosys_text, int mode, char* buf, size_t cap, size_t* needed) {
+    std::string s;
+    return guarded([&] { s = preprocess_yosys(yosys_text ? yosys_text : "", (mode & 1) != 0, (mode & 2) != 0); }) || emit(s, buf, cap, needed);
+}
+
+int hh_preprocess_assign_dict(const char* yosys_text, int arith, char* buf, size_t cap, size_t* needed) {
+    std::string s;
+    return guarded([&] { s = preprocess_assign_dict(yosys_text ? yosys_text : "", arith != 0); }) || emit(s, buf, cap, needed);
+}
+
 int hh_read_input_csv(const char* path, const char* ptxt_type, char* buf, size_t cap, size_t* needed) {
     std::string s;
     return guarded([&] { s = format_values(read_input_wires(path, ptxt_type ? ptxt_type : "bool")); }) || emit(s, buf, cap, needed);

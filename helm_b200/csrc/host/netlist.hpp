@@ -63,7 +63,11 @@ Ptxt parse_input_wire(const std::string& text, const std::string& ptxt_type);   
 std::string hex_to_bitstring(const std::string& hex);                              // src/lib.rs:183-194
 void expand_bus_value(const std::string& wire, const std::string& hex, size_t width, WireValues* out);
 void write_output_wires(const std::string& file_name, const WireValues& values);
-// Yosys gate-cell netlist -> HELM netlist text (preprocess.cpp; reference hdl-benchmarks/src/lib.rs)
-std::string preprocess_yosys_gates(const std::string& yosys_text);
+// Yosys netlist -> HELM netlist text (preprocess.cpp; reference hdl-benchmarks/src/lib.rs): gate cells, both LUT
+// spellings, multi-bit assigns; arith = true keeps multi-bit nets whole and turns `assign y = a + b` into `add` cells
+std::string preprocess_yosys(const std::string& yosys_text, bool arith, bool exact_consts = false);
+std::string preprocess_yosys_gates(const std::string& yosys_text);       // = preprocess_yosys(text, false)
+// per-bit assign dictionary, "dest=source" lines (reference build_assign_dict, lib.rs:319-391)
+std::string preprocess_assign_dict(const std::string& yosys_text, bool arith);
 
 }  // namespace helm

@@ -30,7 +30,7 @@ class HbGate(C.Structure):
 class HbStats(C.Structure):
     _fields_ = [("pbs_count", C.c_uint64), ("ks_count", C.c_uint64), ("levels", C.c_uint64),
                 ("pbs_ms", C.c_double), ("ks_ms", C.c_double), ("kernel_launches", C.c_uint64),
-                ("pbs_ms_total", C.c_double), ("ks_ms_total", C.c_double)]
+                ("pbs_ms_total", C.c_double), ("ks_ms_total", C.c_double), ("gap_ms_total", C.c_double)]
 
 
 GATE_DTYPE = np.dtype([("op", np.uint8), ("arity", np.uint8), ("flags", np.uint16), ("in", np.uint32, (4,)),

@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libhelm_host.so")
 EXPORTS = ["hh_last_error", "hh_circuit_load", "hh_circuit_load_text", "hh_circuit_free", "hh_circuit_count",
-           "hh_circuit_level_width", "hh_circuit_describe", "hh_circuit_eval_plain", "hh_read_input_csv", "hh_preprocess_yosys",
+           "hh_circuit_level_width", "hh_circuit_describe", "hh_circuit_eval_plain", "hh_read_input_csv", "hh_preprocess_yosys", "hh_preprocess_yosys_mode", "hh_preprocess_assign_dict",
            "hh_session_create", "hh_session_free", "hh_session_run", "hh_session_run_arith", "hh_session_stats"]
 _LIB = None
 
@@ -38,6 +38,8 @@ def lib():
         L.hh_circuit_eval_plain.argtypes = [vp, cp, cp, C.c_int, vp, sz, C.POINTER(sz)]
         L.hh_read_input_csv.argtypes = [cp, cp, vp, sz, C.POINTER(sz)]
         L.hh_preprocess_yosys.argtypes = [cp, vp, sz, C.POINTER(sz)]
+        L.hh_preprocess_yosys_mode.argtypes = [cp, C.c_int, vp, sz, C.POINTER(sz)]
+        L.hh_preprocess_assign_dict.argtypes = [cp, C.c_int, vp, sz, C.POINTER(sz)]
         L.hh_session_create.argtypes = [cp, C.c_int, C.c_uint64, vp, vp, vp, sz, vp, sz, C.POINTER(vp)]
         L.hh_session_free.argtypes = [vp]
         L.hh_session_run.argtypes = [vp, vp, cp, C.c_int, C.c_int, C.c_int, vp, sz, C.POINTER(sz), C.POINTER(C.c_double)]
@@ -58,9 +60,9 @@ def _text(call):
     cap = 1 << 16
     while True:
         buf = C.create_string_buffer(cap)
-        need = C.c_size_t()
+        need = C.c_size_t(0)
         rc = call(buf, cap, C.byref(need))
-        if rc == 2 and need.value > cap:
+        if rc != 0 and need.value > cap:      # the text did not fit: grow and call again
             cap = need.value + 16
             continue
         _ck(rc)
@@ -82,10 +84,19 @@ def _fmt(values):
                    for k, v in values.items()).encode()
 
 
-def preprocess_yosys(text):
-    """Yosys gate-cell netlist text -> HELM netlist text (reference hdl-benchmarks preprocessor)."""
+def preprocess_yosys(text, arith=False, exact_consts=False):
+    """Yosys netlist text -> HELM netlist text (reference hdl-benchmarks preprocessor: gate cells, LUTs, multi-bit
+    assigns; arith=True for arithmetic designs; exact_consts=True turns the reference's LUT-constant quirk off)."""
     L = lib()
-    return _text(lambda b, c, n: L.hh_preprocess_yosys(text.encode(), b, c, n))
+    mode = (1 if arith else 0) | (2 if exact_consts else 0)
+    return _text(lambda b, c, n: L.hh_preprocess_yosys_mode(text.encode(), mode, b, c, n))
+
+
+def preprocess_assign_dict(text, arith=False):
+    """Per-bit assign dictionary {dest: source} (reference build_assign_dict)."""
+    L = lib()
+    txt = _text(lambda b, c, n: L.hh_preprocess_assign_dict(text.encode(), int(arith), b, c, n))
+    return dict(line.split("=", 1) for line in txt.splitlines() if line)
 
 
 def read_input_wires(path, ptxt_type="bool"):

@@ -64,6 +64,7 @@ typedef struct {
     double pbs_ms, ks_ms;               /* device time of the last hb_eval_level / batch call */
     uint64_t kernel_launches;           /* engine kernels launched since context creation */
     double pbs_ms_total, ks_ms_total;   /* device time summed over every hb_eval_level since creation */
+    double gap_ms_total;                /* stream time between consecutive batches' kernels (job upload, launch gaps) */
 } hb_stats_t;
 
 hb_status hb_ctx_create(int32_t device, hb_ctx** out);

@@ -36,6 +36,15 @@ int hh_circuit_eval_plain(const hh_circuit*, const char* inputs, const char* ptx
 /* Yosys structural Verilog (gate cells) -> HELM netlist text: the hdl-benchmarks preprocessor for gate netlists
  * (reference hdl-benchmarks/src/lib.rs:319-391, 608-810; how c880 / c7552 of BASELINE.json configs[1] are produced) */
 int hh_preprocess_yosys(const char* yosys_text, char* buf, size_t cap, size_t* needed);
+/* the same with mode bits.  HH_PP_ARITH: the reference's `arith` switch (convert_verilog(..., arith), lib.rs:392-398) --
+ * multi-bit nets stay whole and `assign y = a + b;` becomes `add a<id>(a, b, y);`.  HH_PP_EXACT_CONSTS: write the LUT
+ * constants Yosys wrote; without it the reference's own reading is reproduced, which cuts `assign`-spelled hex constants
+ * at every 'd' digit (8'hd0 -> 0x0; lib.rs:511-514) -- its checked-in *_lut*.v netlists carry those constants. */
+enum { HH_PP_ARITH = 1, HH_PP_EXACT_CONSTS = 2 };
+int hh_preprocess_yosys_mode(const char* yosys_text, int mode, char* buf, size_t cap, size_t* needed);
+/* the per-bit assign dictionary as "dest=source" lines (build_assign_dict, hdl-benchmarks/src/lib.rs:319-391; the
+ * reference tests it directly, hdl-benchmarks/tests/preprocessor_test.rs:8-250) */
+int hh_preprocess_assign_dict(const char* yosys_text, int arith, char* buf, size_t cap, size_t* needed);
 /* CSV helper (reference read_input_wires): file -> "wire=value\n" lines */
 int hh_read_input_csv(const char* path, const char* ptxt_type, char* buf, size_t cap, size_t* needed);
 

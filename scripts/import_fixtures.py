@@ -7,12 +7,15 @@ import os, shutil, sys
 SRC = "/root/reference/hdl-benchmarks"
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 NETS = ["processed-netlists/" + f for f in ("s27.v", "2-bit-adder.v", "c17.v", "16-bit-mult-gates.v", "8-bit-adder-lut-2-1.v",
-        "8-bit-adder-lut-3-1.v", "chi_squared_arith.v", "invalid.v", "gates.v", "c17_lut_2.v")] + \
-       ["netlists/c880.v", "netlists/c7552.v", "netlists/c17.v"]
+        "8-bit-adder-lut-3-1.v", "chi_squared_arith.v", "invalid.v", "gates.v", "c17_lut_2.v", "c17_lut_4.v", "c880_lut_4.v",
+        "c7552_lut_4.v")] + \
+       ["netlists/" + f for f in ("c880.v", "c7552.v", "c17.v", "c17_lut_4.v", "c880_lut_4.v", "c7552_lut_4.v",
+        "lut-multibit-input-test.v", "8-bit-adder-lut.v", "c1355-lut-2-1.v", "c1355.v", "s27.v", "s386.v",
+        "16-bit-mult-gates.v")] + ["designs/chi_squared.v"]
 CASES = ["2-bit-adder.inputs.csv", "2-bit-adder.outputs.csv", "8-bit-adder.inputs.csv", "bool_array.input.csv",
          "16-bit-mult.inputs.csv"] + ["chi_squared_arith_%d.%s.csv" % (i, k) for i in range(1, 5) for k in ("inputs", "outputs")]
 for rel in NETS:
-    sub = "yosys" if rel.startswith("netlists/") else "netlists"
+    sub = "yosys" if rel.startswith(("netlists/", "designs/")) else "netlists"
     dst = os.path.join(ROOT, "tests", "golden", sub)
     os.makedirs(dst, exist_ok=True)
     shutil.copy(os.path.join(SRC, rel), dst)
