@@ -189,15 +189,16 @@ def hbm_peak_gbs():
         return 6650.0        # fallback stated in B200_PROFILING.md
 
 
-def iscas_latency(name, device):
-    """End-to-end latency of one ISCAS'85 netlist in gates mode (all-false inputs, the reference README invocation):
-    evaluate = every level as one hb_eval_level batch, wires resident; outputs checked against the plaintext netlist."""
+def iscas_latency(name, device, params=PARAM_SET):
+    """End-to-end latency of one ISCAS'85 netlist (all-false inputs, the reference README invocation) in gates mode
+    (boolean parameters) or LUT mode (a `_lut` netlist under a shortint parameter set): evaluate = every level as one
+    hb_eval_level batch, wires resident; outputs checked against the plaintext netlist."""
     from helm_b200 import host as H
     path = os.path.join(ROOT, "tests", "golden", "yosys", name + ".v")
     if not os.path.exists(path):
         return None
-    circ = H.Circuit(text=H.preprocess_yosys(open(path).read()))
-    sess = H.Session(PARAM_SET, device=device, seed=5)
+    circ = H.Circuit(text=H.preprocess_yosys(open(path).read(), exact_consts=True))
+    sess = H.Session(params, device=device, seed=5)
     want = circ.evaluate()
     best = None
     for rep in range(3):
@@ -207,7 +208,7 @@ def iscas_latency(name, device):
     widths = circ.level_widths()
     pbs = circ.count(H.Circuit.PBS_GATES) + sum(1 for g in circ.gates() if g[1] == "mux")
     sess.close()
-    return {"netlist": name, "levels": len(widths), "max_width": max(widths), "pbs": pbs,
+    return {"netlist": name, "params": params, "levels": len(widths), "max_width": max(widths), "pbs": pbs,
             "evaluate_ms": 1e3 * best[1], "encrypt_ms": 1e3 * best[0], "decrypt_ms": 1e3 * best[2],
             "pbs_per_s": pbs / best[1], "inputs": "all false", "outputs_verified": True}
 
@@ -392,9 +393,10 @@ def main():
 
     # ---- BASELINE.json metric, second half: c7552 gates-mode end-to-end latency (configs[1]) through the host library
     # (Yosys netlist -> restated preprocessor -> levelizer -> one hb_eval_level per level), N = 1 only
-    c7552 = None
+    c7552 = c7552_lut = None
     if rank == 0 and world == 1 and not args.no_latency:
         c7552 = iscas_latency("c7552", local)
+        c7552_lut = iscas_latency("c7552_lut_4", local, "shortint_m2c2")
 
     if rank == 0:
         value = W * args.steps / (ms_total * 1e-3)
@@ -417,7 +419,7 @@ def main():
                              "flops_per_launch": flops_per_launch, "kernel_ms": pbs_ms, "ks_kernel_ms": ks_ms, "gap_ms": gap_ms,
                              "hbm_floor_ms": 1e3 * (bsk_bytes + 3.0 * Wr * words * 4) / (hbm_peak_gbs() * 1e9)},
                 "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
-                "verified": verified, "c7552_gates_mode": c7552}
+                "verified": verified, "c7552_gates_mode": c7552, "c7552_lut_mode": c7552_lut}
         emit_line(line)
     wires.close()
     eng.close()

@@ -118,3 +118,32 @@ def _m2c2():
     if not _M2C2:
         _M2C2.append(H.Session("shortint_m2c2", seed=21))
     return _M2C2[0]
+
+
+WIDE = """module m (a, b, y0, y1, y2, y3, y4, y5);
+  input [7:0] a;
+  input [7:0] b;
+  output [7:0] y0;
+  add g0(a, b, y0);
+  sub g1(a, b, y1);
+  mult g2(a, b, y2);
+  shr g3(y2, 9, y3);
+  mult g4(y1, 1000003, y4);
+  add g5(y4, 18446744073709551557, y5);
+endmodule
+"""
+
+
+@pytest.mark.parametrize("ptxt_type", ["u64", "u128"])
+def test_wide_integer_types(toy_session, ptxt_type):
+    """FheUint64 / FheUint128 (reference src/gates.rs:386-600 dispatches on the plaintext type): 32 and 64 radix blocks."""
+    from helm_b200 import host as H
+    c = H.Circuit(text=WIDE, is_arith=True)
+    bits = int(ptxt_type[1:])
+    ins = {"a": (1 << bits) - 3, "b": (1 << (bits - 1)) + 12345}
+    want = c.evaluate(ins, ptxt_type)
+    assert want["y2"] == (ins["a"] * ins["b"]) % (1 << bits)                 # the plaintext evaluator itself
+    got, secs, cnt = toy_session.run_arith(c, ins, ptxt_type, all_wires=True)
+    for w in want:
+        assert got[w] == want[w], (ptxt_type, w, got[w], want[w])
+    print("%s: %d bootstraps in %d batches, evaluate %.3f s" % (ptxt_type, cnt["bootstraps"], cnt["batches"], secs[1]))
