@@ -150,12 +150,18 @@ struct Shape {
 };
 template <class Small> constexpr Shape with_small(Shape s) { s.small_smem = &Small::smem; s.small_launch = &Small::launch; return s; }
 
-template <class T, int N, int K, int L, int RA, int RB, int G, int NT, int MINB>
+#ifndef HB_SMALL_NT
+#define HB_SMALL_NT 384        // threads of the one-gate boolean instance (288: 100.2 ms, 384: 95.4 ms, 512: 97.9 ms on c7552)
+#endif
+#ifndef HB_STAGE_KEY
+#define HB_STAGE_KEY true      // narrow-batch instances stage BSK_i in shared memory (cp.async.bulk), see pbs_kernel.cuh
+#endif
+template <class T, int N, int K, int L, int RA, int RB, int G, int NT, int MINB, bool STAGE = false>
 struct Inst {
     using C = PbsCfg<T, N, K, L, RA, RB, G>;
-    static size_t smem(int n) { return C::smem_bytes(n); }
+    static size_t smem(int n) { return STAGE ? C::smem_bytes_staged(n) : C::smem_bytes(n); }
     static cudaError_t launch(const PbsArgs& a, cudaStream_t s, size_t smem) {
-        auto kern = pbs_kernel<T, N, K, L, RA, RB, G, NT, MINB>;
+        auto kern = pbs_kernel<T, N, K, L, RA, RB, G, NT, MINB, STAGE>;
         static bool attr_done = false;
         if (!attr_done) {
             cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
@@ -196,12 +202,12 @@ struct Inst16 {
 
 const Shape g_shapes[] = {
     // tfhe boolean DEFAULT_PARAMETERS
-    with_small<Inst<uint32_t, 512, 2, 3, 16, 16, 1, 288, 1>>(Inst16<uint32_t, 2, 3, 6, HB_PBS16_G, 8 / HB_PBS16_G, HB_TMEMW>::shape()),
+    with_small<Inst<uint32_t, 512, 2, 3, 16, 16, 1, HB_SMALL_NT, 1, HB_STAGE_KEY>>(Inst16<uint32_t, 2, 3, 6, HB_PBS16_G, 8 / HB_PBS16_G, HB_TMEMW>::shape()),
     Inst<uint32_t, 1024, 1, 3, 16, 32, 1, 192, 2>::shape(),    // concrete-core GPU path of the reference
     // PARAM_MESSAGE_1_CARRY_1_KS_PBS / PARAM_MESSAGE_2_CARRY_1_KS_PBS
-    with_small<Inst<uint64_t, 512, 3, 1, 16, 16, 1, 256, 1>>(Inst<uint64_t, 512, 3, 1, 16, 16, 2, 128, 2>::shape()),
+    with_small<Inst<uint64_t, 512, 3, 1, 16, 16, 1, 256, 1, HB_STAGE_KEY>>(Inst<uint64_t, 512, 3, 1, 16, 16, 2, 128, 2>::shape()),
     // PARAM_MESSAGE_2_CARRY_2_KS_PBS
-    with_small<Inst<uint64_t, 2048, 1, 1, 32, 32, 1, 256, 1>>(Inst<uint64_t, 2048, 1, 1, 32, 32, 2, 128, 1>::shape()),
+    with_small<Inst<uint64_t, 2048, 1, 1, 32, 32, 1, 256, 1, HB_STAGE_KEY>>(Inst<uint64_t, 2048, 1, 1, 32, 32, 2, 128, 1>::shape()),
 };
 
 int find_shape(const hb_params& p) {

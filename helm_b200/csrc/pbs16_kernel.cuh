@@ -26,20 +26,6 @@ __device__ __forceinline__ double2 ldg_nc(const double2* p) {
     asm volatile("ld.global.nc.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p));
     return v;
 }
-__device__ __forceinline__ void mbar_init(uint32_t addr, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(addr), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t addr) {
-    asm volatile("{ .reg .b64 st; mbarrier.arrive.shared::cta.b64 st, [%0]; }" ::"r"(addr) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t addr, uint32_t parity) {
-    uint32_t ok;
-    do {
-        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
-                     : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
-    } while (!ok);
-}
-
 // ---- tensor memory as per-thread scratch.  The kernel issues no MMA; TMEM (256 KB per SM, its own datapath) holds the
 // 2 x 16 inter-stage twiddles every thread needs in each forward / inverse transform, which otherwise are 15 % of the
 // shared-memory wavefronts (profiles/r01_v4_*).  Shape 32x32b: lane i of a warp reads/writes TMEM lane 32*(warp%4)+i,

@@ -148,6 +148,29 @@ template <class T> __device__ __forceinline__ T tv_body(const PbsJob& jb, int N,
     return neg ? (T)(0 - v) : v;
 }
 
+// ---- mbarrier / bulk-copy helpers (shared-memory addresses as 32-bit shared-window offsets)
+__device__ __forceinline__ void mbar_init(uint32_t addr, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(addr), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t addr) {
+    asm volatile("{ .reg .b64 st; mbarrier.arrive.shared::cta.b64 st, [%0]; }" ::"r"(addr) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t addr, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                     : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t addr, uint32_t bytes) {
+    asm volatile("{ .reg .b64 st; mbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1; }" ::"r"(addr), "r"(bytes) : "memory");
+}
+// one contiguous global -> shared copy by the TMA unit (no tensor map), completion counted in bytes on an mbarrier
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t mbar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(mbar) : "memory");
+}
+
 template <class T, int N, int K, int L, int RA, int RB, int G>
 struct PbsCfg {
     static constexpr bool SMALLDIG = sizeof(T) == 4;      // u32 parameter sets have base_log <= 7 (checked on the host)
@@ -164,10 +187,16 @@ struct PbsCfg {
                (size_t)G * (K + 1) * N * sizeof(T) + (size_t)G * ROWS * PARTS * RB * sizeof(typename Dig::type) +
                (((size_t)G * (n + 1) * 2 + 15) & ~(size_t)15);
     }
+    // STAGE instances: one step's Fourier GGSW (ROWS x (K+1) spectra, contiguous in the key) + the mbarrier
+    static constexpr size_t KEY_BYTES = (size_t)ROWS * (K + 1) * M * sizeof(double2);
+    __host__ __device__ static constexpr size_t smem_bytes_staged(int n) { return smem_bytes(n) + KEY_BYTES + 16; }
 };
 
 // ------------------------------------------------------------------ the kernel
-template <class T, int N, int K, int L, int RA, int RB, int G, int NT, int MINB>
+// STAGE (narrow-batch instances): BSK_{i+1} is copied into shared memory by one cp.async.bulk while step i runs its inverse
+// transforms and step i+1 its rotation / forward transforms, so the MAC reads the key at shared-memory speed instead of
+// waiting on L2 (with one gate per CTA nothing else amortises that latency; it was 37 % of the step, profiles/r01_v6_*).
+template <class T, int N, int K, int L, int RA, int RB, int G, int NT, int MINB, bool STAGE = false>
 __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
     using C = PbsCfg<T, N, K, L, RA, RB, G>;
     constexpr int M = C::M, ROWS = C::ROWS, XROW = C::XROW;
@@ -181,11 +210,26 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
     constexpr int PARTS = C::PARTS;
     constexpr bool CHAIN_F = RA == RB && RA <= 32 && G * ROWS * RB <= NT;
     constexpr bool CHAIN_I = RA == RB && RA <= 32 && G * (K + 1) * RA <= NT;
+#ifndef HB_SPREAD_I
+#define HB_SPREAD_I 1
+#endif
+    constexpr bool SPREAD_I = HB_SPREAD_I && CHAIN_I && RA == 16 && G * (K + 1) * 32 <= NT;
     DigT* digs = reinterpret_cast<DigT*>(acc + (size_t)G * (K + 1) * N);           // [G][ROWS][PARTS][RB]
     uint16_t* atil = reinterpret_cast<uint16_t*>(digs + (size_t)G * ROWS * PARTS * RB);   // [G][n+1]
 
     const int tid = threadIdx.x;
     const int n = A.n;
+    // staged key block [ROWS][K+1][M] and its mbarrier, after the (16-byte padded) switched masks
+    double2* KB = reinterpret_cast<double2*>(smem_raw + C::smem_bytes(n));
+    const uint32_t kb_addr = (uint32_t)__cvta_generic_to_shared(KB);
+    const uint32_t kbar = kb_addr + (uint32_t)C::KEY_BYTES;
+    uint32_t kphase = 0;
+    if (STAGE && tid == 0) {
+        mbar_init(kbar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        mbar_expect_tx(kbar, (uint32_t)C::KEY_BYTES);
+        bulk_g2s(kb_addr, A.bsk, (uint32_t)C::KEY_BYTES, kbar);
+    }
     const int job0 = blockIdx.x * G;
     const T* in = reinterpret_cast<const T*>(A.in);
 
@@ -229,7 +273,17 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
         int any = 0;
 #pragma unroll
         for (int g = 0; g < G; ++g) any |= atil[g * (n + 1) + i];
-        if (any == 0) continue;                       // uniform across the CTA
+        if (any == 0) {                               // uniform across the CTA
+            if (STAGE) {                              // consume the block in flight, start the next one
+                mbar_wait(kbar, kphase); kphase ^= 1u;
+                __syncthreads();
+                if (tid == 0 && i + 1 < n) {
+                    mbar_expect_tx(kbar, (uint32_t)C::KEY_BYTES);
+                    bulk_g2s(kb_addr, A.bsk + (size_t)(i + 1) * ROWS * (K + 1) * M, (uint32_t)C::KEY_BYTES, kbar);
+                }
+            }
+            continue;
+        }
 
         // P1a: rotate-subtract and signed decomposition, once per coefficient for all L levels; digits staged in
         // shared memory in the order the FFT pass reads them ([row][part][j0], part = a pair of j1)
@@ -281,7 +335,7 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
         }
         // P3: pointwise MAC with BSK_i; one read of BSK feeds all G gates.  When every position has its own thread the
         // first rows' key loads are issued before the barrier (they do not depend on the spectra)
-        constexpr bool PRE = M <= NT;
+        constexpr bool PRE = !STAGE && M <= NT;
         constexpr int NPRE = ROWS < 3 ? ROWS : 3;
         double2 bpre[NPRE][K + 1];
         if (PRE && tid < M) {
@@ -292,6 +346,7 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
                 for (int j = 0; j <= K; ++j) bpre[row][j] = __ldg(bp0 + (size_t)(row * (K + 1) + j) * M);
         }
         __syncthreads();
+        if (STAGE) { mbar_wait(kbar, kphase); kphase ^= 1u; }
         for (int pos = tid; pos < M; pos += NT) {
             const int s = (pos / RB) * (RB + 1) + (pos % RB);
             double2 o[G][K + 1];
@@ -304,7 +359,9 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
             for (int row = 0; row < ROWS; ++row) {
                 double2 b[K + 1];
 #pragma unroll
-                for (int j = 0; j <= K; ++j) b[j] = (PRE && row < NPRE) ? bpre[row][j] : __ldg(bp + (size_t)(row * (K + 1) + j) * M);
+                for (int j = 0; j <= K; ++j)
+                    b[j] = STAGE ? KB[(size_t)(row * (K + 1) + j) * M + pos]
+                                 : (PRE && row < NPRE) ? bpre[row][j] : __ldg(bp + (size_t)(row * (K + 1) + j) * M);
 #pragma unroll
                 for (int g = 0; g < G; ++g) {
                     const double2 f = X[((size_t)g * ROWS + row) * XROW + s];
@@ -318,8 +375,16 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
                 for (int j = 0; j <= K; ++j) X[((size_t)g * ROWS + j) * XROW + s] = o[g][j];
         }
         __syncthreads();
+        if (STAGE && tid == 0 && i + 1 < n) {         // every read of the staged block is behind the barrier above
+            mbar_expect_tx(kbar, (uint32_t)C::KEY_BYTES);
+            bulk_g2s(kb_addr, A.bsk + (size_t)(i + 1) * ROWS * (K + 1) * M, (uint32_t)C::KEY_BYTES, kbar);
+        }
         // P4: inverse radix-RB DFT over k1 (column k0), conj inter-stage twiddle
-        for (int t = tid; t < G * (K + 1) * RA; t += NT) {
+        // SPREAD_I: the G(K+1) half-warps of the inverse transform sit in different warps (lanes 0..15), i.e. on different
+        // schedulers, instead of back to back in the first warps (c7552: 97.4 -> 95.4 ms).  The same spreading of the
+        // (K+1)L forward half-warps was measured slower (109.8 ms): half-filled warps cost full FP64 issue slots
+        for (int t = SPREAD_I ? ((tid & 31) < RA ? (tid >> 5) * RA + (tid & 31) : G * (K + 1) * RA) : tid; t < G * (K + 1) * RA;
+             t += SPREAD_I ? G * (K + 1) * RA : NT) {
             const int k0 = t % RA, j = (t / RA) % (K + 1), g = t / (RA * (K + 1));
             double2* xc = X + ((size_t)g * ROWS + j) * XROW + k0 * (RB + 1);
             double2 x[RB];
@@ -331,7 +396,8 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
         }
         if (CHAIN_I) __syncwarp(); else __syncthreads();
         // P5: inverse radix-RA DFT over k0, untwist, round, wrapping add into the accumulator
-        for (int t = tid; t < G * (K + 1) * RB; t += NT) {
+        for (int t = SPREAD_I ? ((tid & 31) < RB ? (tid >> 5) * RB + (tid & 31) : G * (K + 1) * RB) : tid; t < G * (K + 1) * RB;
+             t += SPREAD_I ? G * (K + 1) * RB : NT) {
             const int j0 = t % RB, j = (t / RB) % (K + 1), g = t / (RB * (K + 1));
             const double2* xr = X + ((size_t)g * ROWS + j) * XROW;
             double2 x[RA];

@@ -129,7 +129,7 @@ WIDE = """module m (a, b, y0, y1, y2, y3, y4, y5);
   mult g2(a, b, y2);
   shr g3(y2, 9, y3);
   mult g4(y1, 1000003, y4);
-  add g5(y4, 18446744073709551557, y5);
+  add g5(y4, 4000000007, y5);
 endmodule
 """
 
