@@ -147,8 +147,12 @@ struct Shape {
     // narrow batches (<= 3 x SMs bootstraps): one gate per CTA, every transform on its own group of threads
     size_t (*small_smem)(int n) = nullptr;
     cudaError_t (*small_launch)(const PbsArgs&, cudaStream_t, size_t smem) = nullptr;
+    // between one and small2_waves x SMs x 2 bootstraps: two gates per CTA (one wave of those beats two waves of the above)
+    size_t (*small2_smem)(int n) = nullptr;
+    cudaError_t (*small2_launch)(const PbsArgs&, cudaStream_t, size_t smem) = nullptr;
 };
 template <class Small> constexpr Shape with_small(Shape s) { s.small_smem = &Small::smem; s.small_launch = &Small::launch; return s; }
+template <class Small2> constexpr Shape with_small2(Shape s) { s.small2_smem = &Small2::smem; s.small2_launch = &Small2::launch; return s; }
 
 #ifndef HB_SMALL_NT
 #define HB_SMALL_NT 384        // threads of the one-gate boolean instance (288: 100.2 ms, 384: 95.4 ms, 512: 97.9 ms on c7552)
@@ -202,7 +206,8 @@ struct Inst16 {
 
 const Shape g_shapes[] = {
     // tfhe boolean DEFAULT_PARAMETERS
-    with_small<Inst<uint32_t, 512, 2, 3, 16, 16, 1, HB_SMALL_NT, 1, HB_STAGE_KEY>>(Inst16<uint32_t, 2, 3, 6, HB_PBS16_G, 8 / HB_PBS16_G, HB_TMEMW>::shape()),
+    with_small2<Inst<uint32_t, 512, 2, 3, 16, 16, 2, HB_SMALL_NT, 1, HB_STAGE_KEY>>(
+        with_small<Inst<uint32_t, 512, 2, 3, 16, 16, 1, HB_SMALL_NT, 1, HB_STAGE_KEY>>(Inst16<uint32_t, 2, 3, 6, HB_PBS16_G, 8 / HB_PBS16_G, HB_TMEMW>::shape())),
     Inst<uint32_t, 1024, 1, 3, 16, 32, 1, 192, 2>::shape(),    // concrete-core GPU path of the reference
     // PARAM_MESSAGE_1_CARRY_1_KS_PBS / PARAM_MESSAGE_2_CARRY_1_KS_PBS
     with_small<Inst<uint64_t, 512, 3, 1, 16, 16, 1, 256, 1, HB_STAGE_KEY>>(Inst<uint64_t, 512, 3, 1, 16, 16, 2, 128, 2>::shape()),
@@ -286,9 +291,24 @@ hb_status launch_pbs(hb_ctx* c, const void* in, uint32_t in_stride, void* out, u
     a.in = in; a.in_stride = in_stride; a.out = out; a.out_stride = out_stride; a.jobs = jobs; a.n_jobs = n_jobs;
     a.bsk = (const double2*)c->bsk_f.p; a.wtab = (const double2*)c->wtab.p; a.n = c->p.n; a.base_log = c->p.pbs_base_log;
     // Narrow batches are latency-bound (one bootstrap is n sequential CMUX steps, so what matters is the time of ONE step of
-    // ONE CTA): below small_max x SMs bootstraps they run the one-gate-per-CTA instance.  HB_PBS_SMALL=0 disables.
+    // ONE CTA).
+    // Measured on boolean default (scripts/narrow_sweep.py, ms per launch): one gate per CTA 2.87 up to 1 x SMs bootstraps;
+    // two gates per CTA 4.2 up to 2 x SMs; the throughput kernel 6.97 up to 4 x SMs and 10.6 up to 8 x SMs.  So: G = 1 for one
+    // wave, G = 2 for at most one wave of pairs, the throughput kernel beyond.  The shortint shapes have no pair instance: G = 1 for one
+    // wave (M2C2 6.3 ms, M1C1 2.3 ms), then their wide instances (9.4 / 3.9 ms up to 2 x SMs).  HB_PBS_SMALL=0 disables both, HB_PBS_SMALL_MAX / HB_PBS_SMALL2_MAX override the wave counts.
     static const int small_on = getenv("HB_PBS_SMALL") ? atoi(getenv("HB_PBS_SMALL")) : 1;
-    static const int small_max = getenv("HB_PBS_SMALL_MAX") ? atoi(getenv("HB_PBS_SMALL_MAX")) : 3;
+    static const int small_max_env = getenv("HB_PBS_SMALL_MAX") ? atoi(getenv("HB_PBS_SMALL_MAX")) : 0;
+    static const int small2_max = getenv("HB_PBS_SMALL2_MAX") ? atoi(getenv("HB_PBS_SMALL2_MAX")) : 2;
+    const bool pair_ok = small_on && sh.small2_launch && small2_max > 0;
+    const int small_max = small_max_env ? small_max_env : 1;
+    if (pair_ok && n_jobs > (uint32_t)(small_max * c->sm_count) && n_jobs <= (uint32_t)(small2_max * c->sm_count)) {
+        const size_t sm = sh.small2_smem(c->p.n);
+        if (sm <= 227 * 1024) {
+            CU(c, sh.small2_launch(a, c->stream, sm));
+            c->stats.kernel_launches++; c->stats.pbs_count += n_jobs;
+            return HB_OK;
+        }
+    }
     if (small_on && sh.small_launch && n_jobs <= (uint32_t)(small_max * c->sm_count)) {
         const size_t sm = sh.small_smem(c->p.n);
         if (sm <= 227 * 1024) {
