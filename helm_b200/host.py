@@ -55,9 +55,9 @@ def _ck(rc):
         raise HostError(lib().hh_last_error().decode())
 
 
-def _text(call):
-    """Runs call(buf, cap, needed) growing the buffer until the text fits."""
-    cap = 1 << 16
+def _text(call, cap=1 << 16):
+    """Runs call(buf, cap, needed) growing the buffer until the text fits (the call is repeated then: callers whose call
+    does real work pass a cap that holds their largest answer)."""
     while True:
         buf = C.create_string_buffer(cap)
         need = C.c_size_t(0)
@@ -177,7 +177,7 @@ class Session:
         """encrypt_inputs -> evaluate_encrypted x cycles -> decrypt_outputs.  Returns (values, seconds[3])."""
         secs = (C.c_double * 3)()
         txt = _text(lambda b, c, n: self.L.hh_session_run(self.h, circuit.h, _fmt(inputs), cycles, int(all_wires),
-                                                          int(verbose), b, c, n, secs))
+                                                          int(verbose), b, c, n, secs), cap=1 << 22)
         return _parse(txt), list(secs)
 
     def run_arith(self, circuit, inputs=None, ptxt_type="u32", cycles=1, all_wires=False, verbose=False):
@@ -185,7 +185,7 @@ class Session:
         secs = (C.c_double * 3)()
         cnt = (C.c_uint64 * 2)()
         txt = _text(lambda b, c, n: self.L.hh_session_run_arith(self.h, circuit.h, _fmt(inputs), ptxt_type.encode(), cycles,
-                                                                int(all_wires), int(verbose), b, c, n, secs, cnt))
+                                                                int(all_wires), int(verbose), b, c, n, secs, cnt), cap=1 << 22)
         return _parse(txt), list(secs), {"bootstraps": int(cnt[0]), "batches": int(cnt[1])}
 
     def stats(self):

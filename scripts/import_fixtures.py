@@ -23,4 +23,18 @@ dst = os.path.join(ROOT, "tests", "golden", "test-cases")
 os.makedirs(dst, exist_ok=True)
 for f in CASES:
     shutil.copy(os.path.join(SRC, "test-cases", f), dst)
-print("imported", len(NETS), "netlists and", len(CASES), "csv files")
+# the large benchmark circuits of the reference's test-cases directory, gzip-compressed (1.7 MB of Yosys text each)
+import gzip
+BIG = ["netlists/aes_core_gates.v", "netlists/chi_squared_gates.v", "netlists/v2_euclidean_gates.v", "designs/v2-euclidean-distance.v"]
+BIG_CASES = ["aes.inputs.csv", "chi_squared_bin_1.inputs.csv", "v2-euclidean-distance-bin.inputs.csv", "v2-euclidean-distance.inputs.csv",
+             "32-bit-mult.inputs.csv"]
+for rel in BIG:
+    with open(os.path.join(SRC, rel), "rb") as f, gzip.GzipFile(os.path.join(ROOT, "tests", "golden", "yosys", os.path.basename(rel) + ".gz"), "wb", mtime=0) as g:
+        g.write(f.read())
+with open(os.path.join(SRC, "processed-netlists", "32-bit-mult-gates.v"), "rb") as f, \
+        gzip.GzipFile(os.path.join(ROOT, "tests", "golden", "netlists", "32-bit-mult-gates.v.gz"), "wb", mtime=0) as g:
+    g.write(f.read())
+shutil.copy(os.path.join(SRC, "processed-netlists", "5x5_x_5x5-mmult-arith.v"), os.path.join(ROOT, "tests", "golden", "netlists"))
+for f in BIG_CASES:
+    shutil.copy(os.path.join(SRC, "test-cases", f), dst)
+print("imported", len(NETS) + len(BIG) + 2, "netlists and", len(CASES) + len(BIG_CASES), "csv files")
