@@ -78,18 +78,31 @@ struct Fft {
     int M = 0;
     std::vector<double> wr, wi;      // e^{+2 pi i j / M}, j < M/2
     std::vector<double> tr, ti;      // twist e^{+i pi j / (2M)} = omega^j, omega = e^{i pi / N}
+    std::vector<std::vector<double>> swr, swi;   // per stage (half = M/2, M/4, ... 1): w[j * step], j < half, contiguous
     void init(int M_) {
         M = M_; wr.resize(M / 2); wi.resize(M / 2); tr.resize(M); ti.resize(M);
         for (int j = 0; j < M / 2; ++j) { double a = 2.0 * M_PI * j / M; wr[j] = std::cos(a); wi[j] = std::sin(a); }
+        swr.clear(); swi.clear();
+        for (int half = M / 2, step = 1; half >= 1; half >>= 1, step <<= 1) {
+            std::vector<double> a(half), b(half);
+            for (int j = 0; j < half; ++j) { a[j] = wr[j * step]; b[j] = wi[j * step]; }
+            swr.push_back(a); swi.push_back(b);
+        }
         for (int j = 0; j < M; ++j) { double a = M_PI * j / (2.0 * M); tr[j] = std::cos(a); ti[j] = std::sin(a); }
     }
-    // forward: DIF, natural in -> bit-reversed out, kernel e^{+2 pi i jk/M}
-    void fwd(double* re, double* im) const {
-        for (int half = M / 2, step = 1; half >= 1; half >>= 1, step <<= 1) {
+    // forward: DIF, natural in -> bit-reversed out, kernel e^{+2 pi i jk/M}.  Twiddles are read from one contiguous
+    // table per stage (sw*[stage]) so the j loop vectorises; the arithmetic and its order are those of the plain
+    // strided form (w = wr[j * step]), results are bit-identical
+    void fwd(double* __restrict re, double* __restrict im) const {
+        int stage = 0;
+        for (int half = M / 2; half >= 1; half >>= 1, ++stage) {
+            const double* __restrict twr = swr[stage].data(); const double* __restrict twi = swi[stage].data();
             for (int base = 0; base < M; base += 2 * half) {
-                double* ar = re + base; double* ai = im + base; double* br = ar + half; double* bi = ai + half;
+                double* __restrict ar = re + base; double* __restrict ai = im + base;
+                double* __restrict br = ar + half; double* __restrict bi = ai + half;
+#pragma omp simd
                 for (int j = 0; j < half; ++j) {
-                    double w_r = wr[j * step], w_i = wi[j * step];
+                    double w_r = twr[j], w_i = twi[j];
                     double xr = ar[j] - br[j], xi = ai[j] - bi[j];
                     ar[j] += br[j]; ai[j] += bi[j];
                     br[j] = xr * w_r - xi * w_i; bi[j] = xr * w_i + xi * w_r;
@@ -98,12 +111,16 @@ struct Fft {
         }
     }
     // inverse (unnormalised): DIT, bit-reversed in -> natural out, kernel e^{-2 pi i jk/M}
-    void inv(double* re, double* im) const {
-        for (int half = 1, step = M / 2; half < M; half <<= 1, step >>= 1) {
+    void inv(double* __restrict re, double* __restrict im) const {
+        int stage = (int)swr.size() - 1;
+        for (int half = 1; half < M; half <<= 1, --stage) {
+            const double* __restrict twr = swr[stage].data(); const double* __restrict twi = swi[stage].data();
             for (int base = 0; base < M; base += 2 * half) {
-                double* ar = re + base; double* ai = im + base; double* br = ar + half; double* bi = ai + half;
+                double* __restrict ar = re + base; double* __restrict ai = im + base;
+                double* __restrict br = ar + half; double* __restrict bi = ai + half;
+#pragma omp simd
                 for (int j = 0; j < half; ++j) {
-                    double w_r = wr[j * step], w_i = -wi[j * step];
+                    double w_r = twr[j], w_i = -twi[j];
                     double xr = br[j] * w_r - bi[j] * w_i, xi = br[j] * w_i + bi[j] * w_r;
                     br[j] = ar[j] - xr; bi[j] = ai[j] - xi;
                     ar[j] += xr; ai[j] += xi;
