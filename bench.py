@@ -213,6 +213,43 @@ def iscas_latency(name, device, params=PARAM_SET):
             "pbs_per_s": pbs / best[1], "inputs": "all false", "outputs_verified": True}
 
 
+def iscas_cpu_latency(name):
+    """The same netlist, all-false inputs, evaluated level by level by the CPU oracle (f64-FFT mode, OpenMP one gate per
+    thread = the reference's rayon loop over a level, src/circuit.rs:524-543): the CPU time beside `evaluate_ms`."""
+    from helm_b200 import host as H
+    from oracle import oracle as O
+    path = os.path.join(ROOT, "tests", "golden", "yosys", name + ".v")
+    circ = H.Circuit(text=H.preprocess_yosys(open(path).read(), exact_consts=True))
+    K = O.Keys(PARAM_SET, seed=5)
+    gates = circ.gates()
+    want = circ.evaluate()
+    names = sorted({g[3] for g in gates} | {w for g in gates for w in g[4]})
+    idx = {w: i for i, w in enumerate(names)}
+    wires = np.zeros((len(names), K.params["n"] + 1), dtype=K.dtype)
+    driven = {g[3] for g in gates}
+    prim = [w for w in names if w not in driven]
+    wires[[idx[w] for w in prim]] = K.enc_bool_batch(np.zeros(len(prim), dtype=np.uint8), 77)
+    code = {"and": O.AND, "nand": O.NAND, "or": O.OR, "nor": O.NOR, "xor": O.XOR, "xnor": O.XNOR, "mux": O.MUX,
+            "not": O.NOT, "buf": O.COPY, "dff": O.COPY}
+    levels = {}
+    for lv, ty, _, out, ins in gates:
+        if ty in code:
+            levels.setdefault(lv, []).append((code[ty], idx[ins[0]], idx[ins[1]] if len(ins) > 1 else 0,
+                                              idx[ins[2]] if len(ins) > 2 else 0, idx[out]))
+    K.bool_level(wires, [O.COPY], [0], [0], [0], [0], mode=O.FFT)            # builds the Fourier key outside the timed region
+    t = time.perf_counter()
+    threads = 1
+    for lv in sorted(levels):
+        a = np.array(levels[lv], dtype=np.int64)
+        threads = K.bool_level(wires, a[:, 0], a[:, 1], a[:, 2], a[:, 3], a[:, 4], mode=O.FFT)
+    dt = time.perf_counter() - t
+    outs = [w for w in want if w in idx and w in driven]
+    dec = K.dec_bool_batch(wires[[idx[w] for w in outs]])
+    ok = all(bool(d) == bool(want[w]) for d, w in zip(dec, outs))
+    return {"cpu_evaluate_ms": 1e3 * dt, "cpu_threads": int(threads), "cpu_kind": "port (oracle f64-FFT, one gate per thread per level)",
+            "cpu_outputs_verified": bool(ok)}
+
+
 # ---------------------------------------------------------------- GPU arm
 def main():
     ap = argparse.ArgumentParser()
@@ -396,6 +433,8 @@ def main():
     c7552 = c7552_lut = None
     if rank == 0 and world == 1 and not args.no_latency:
         c7552 = iscas_latency("c7552", local)
+        if c7552 is not None and not args.no_cpu:
+            c7552.update(iscas_cpu_latency("c7552"))
         c7552_lut = iscas_latency("c7552_lut_4", local, "shortint_m2c2")
 
     if rank == 0:
