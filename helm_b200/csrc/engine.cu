@@ -621,6 +621,17 @@ hb_status hb_sync(hb_ctx* c) {
     return HB_OK;
 }
 
+#ifdef HB_PHASE_CLOCKS
+// debug builds only (see pbs_kernel.cuh): cycles per phase of CTA 0 in the last pbs_kernel launch
+hb_status hb_debug_phase_clocks(hb_ctx* c, double* out8) {
+    unsigned long long v[16];
+    CU(c, cudaDeviceSynchronize());
+    CU(c, cudaMemcpyFromSymbol(v, g_phase_clk, sizeof v));
+    for (int q = 0; q < 16; ++q) out8[q] = (double)v[q];
+    return HB_OK;
+}
+#endif
+
 hb_status hb_stats(hb_ctx* c, hb_stats_t* out) {
     if (!c || !out) return HB_ERR_ARG;
     CtxExtra* ex = extra_of(c);

@@ -193,6 +193,19 @@ struct PbsCfg {
 };
 
 // ------------------------------------------------------------------ the kernel
+// -DHB_PHASE_CLOCKS: thread 0 of CTA 0 accumulates clock64() deltas at the phase boundaries of every CMUX step into
+// g_phase_clk (read back with hb_debug_phase_clocks): the critical-path breakdown of the narrow-batch instances, which
+// PC sampling cannot give (most warps idle at barriers most of the time).  Not compiled into the product build.
+#ifdef HB_PHASE_CLOCKS
+__device__ unsigned long long g_phase_clk[16];
+#define HB_PC_DECL unsigned long long pc_t = clock64(), pc_acc[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}
+#define HB_PC_MARK(slot) do { const unsigned long long pc_n = clock64(); pc_acc[slot] += pc_n - pc_t; pc_t = pc_n; } while (0)
+#define HB_PC_FLUSH() do { if (threadIdx.x == 0 && blockIdx.x == 0) for (int q = 0; q < 16; ++q) g_phase_clk[q] = pc_acc[q]; } while (0)
+#else
+#define HB_PC_DECL
+#define HB_PC_MARK(slot)
+#define HB_PC_FLUSH()
+#endif
 // STAGE (narrow-batch instances): BSK_{i+1} is copied into shared memory by one cp.async.bulk while step i runs its inverse
 // transforms and step i+1 its rotation / forward transforms, so the MAC reads the key at shared-memory speed instead of
 // waiting on L2 (with one gate per CTA nothing else amortises that latency; it was 37 % of the step, profiles/r01_v6_*).
@@ -210,6 +223,10 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
     constexpr int PARTS = C::PARTS;
     constexpr bool CHAIN_F = RA == RB && RA <= 32 && G * ROWS * RB <= NT;
     constexpr bool CHAIN_I = RA == RB && RA <= 32 && G * (K + 1) * RA <= NT;
+#ifndef HB_TWCH
+#define HB_TWCH 8
+#endif
+    constexpr int TWCH = HB_TWCH < RA && HB_TWCH < RB ? HB_TWCH : (RA < RB ? RA : RB);   // inter-stage twiddles fetched per batch
 #ifndef HB_SPREAD_I
 #define HB_SPREAD_I 1
 #endif
@@ -269,7 +286,9 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
     __syncthreads();
 
     // ---- n CMUX steps
+    HB_PC_DECL;
     for (int i = 0; i < n; ++i) {
+        HB_PC_MARK(7);
         int any = 0;
 #pragma unroll
         for (int g = 0; g < G; ++g) any |= atil[g * (n + 1) + i];
@@ -303,6 +322,7 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
                 digs[(((size_t)g * ROWS + lev * (K + 1) + r) * PARTS + part) * RB + j0] = Dig::make(dg[0][lev], dg[1][lev], dg[2][lev], dg[3][lev]);
         }
         __syncthreads();
+        HB_PC_MARK(0);
         // P1b: twist, radix-RA DFT over j1, inter-stage twiddle
         for (int t = tid; t < G * ROWS * RB; t += NT) {
             const int j0 = t % RB, grow = t / RB;
@@ -314,14 +334,29 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
                 x[2 * part] = cmul_tw<1>(make_double2(Dig::template get<0>(pk), Dig::template get<1>(pk)), (2 * part) * C::TWA);
                 x[2 * part + 1] = cmul_tw<1>(make_double2(Dig::template get<2>(pk), Dig::template get<3>(pk)), (2 * part + 1) * C::TWA);
             }
+            HB_PC_MARK(8);
             dft_regs<RA, 1>(x);
+            HB_PC_MARK(9);
             double2* xr = X + (size_t)grow * XROW;
+            // twiddle loads are batched ahead of the stores: X and WA share the dynamic shared array, so the compiler must
+            // assume a store to X may change WA and otherwise serialises load -> multiply -> store 16 times (1 180 of the
+            // 7 800 cycles of a boolean step, measured with HB_PHASE_CLOCKS)
 #pragma unroll
-            for (int k0 = 0; k0 < RA; ++k0) xr[k0 * (RB + 1) + j0] = cmul(x[brev<RA>(k0)], WA[k0 * RB + j0]);
+            for (int c0 = 0; c0 < RA; c0 += TWCH) {
+                double2 w[TWCH], y[TWCH];
+#pragma unroll
+                for (int u = 0; u < TWCH; ++u) w[u] = WA[(c0 + u) * RB + j0];
+#pragma unroll
+                for (int u = 0; u < TWCH; ++u) y[u] = cmul(x[brev<RA>(c0 + u)], w[u]);
+#pragma unroll
+                for (int u = 0; u < TWCH; ++u) xr[(c0 + u) * (RB + 1) + j0] = y[u];
+            }
+            HB_PC_MARK(10);
         }
         // the two stages of one row run on the same RA == RB consecutive threads when a single round covers every row:
         // then the transpose only needs a warp-level sync (RA, RB <= 32 divide the warp)
         if (CHAIN_F) __syncwarp(); else __syncthreads();
+        HB_PC_MARK(1);
         // P2: radix-RB DFT over j0 (column k0), in place
         for (int t = tid; t < G * ROWS * RA; t += NT) {
             const int k0 = t % RA, grow = t / RA;
@@ -346,7 +381,9 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
                 for (int j = 0; j <= K; ++j) bpre[row][j] = __ldg(bp0 + (size_t)(row * (K + 1) + j) * M);
         }
         __syncthreads();
+        HB_PC_MARK(2);
         if (STAGE) { mbar_wait(kbar, kphase); kphase ^= 1u; }
+        HB_PC_MARK(3);
         for (int pos = tid; pos < M; pos += NT) {
             const int s = (pos / RB) * (RB + 1) + (pos % RB);
             double2 o[G][K + 1];
@@ -375,6 +412,7 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
                 for (int j = 0; j <= K; ++j) X[((size_t)g * ROWS + j) * XROW + s] = o[g][j];
         }
         __syncthreads();
+        HB_PC_MARK(4);
         if (STAGE && tid == 0 && i + 1 < n) {         // every read of the staged block is behind the barrier above
             mbar_expect_tx(kbar, (uint32_t)C::KEY_BYTES);
             bulk_g2s(kb_addr, A.bsk + (size_t)(i + 1) * ROWS * (K + 1) * M, (uint32_t)C::KEY_BYTES, kbar);
@@ -390,11 +428,23 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
             double2 x[RB];
 #pragma unroll
             for (int k1 = 0; k1 < RB; ++k1) x[k1] = xc[k1];
+            HB_PC_MARK(11);
             dft_regs<RB, -1>(x);
+            HB_PC_MARK(12);
 #pragma unroll
-            for (int j0 = 0; j0 < RB; ++j0) xc[j0] = cmul_conj(x[brev<RB>(j0)], WB[j0 * RA + k0]);
+            for (int c0 = 0; c0 < RB; c0 += TWCH) {              // as in P1b: loads batched ahead of the stores
+                double2 w[TWCH], y[TWCH];
+#pragma unroll
+                for (int u = 0; u < TWCH; ++u) w[u] = WB[(c0 + u) * RA + k0];
+#pragma unroll
+                for (int u = 0; u < TWCH; ++u) y[u] = cmul_conj(x[brev<RB>(c0 + u)], w[u]);
+#pragma unroll
+                for (int u = 0; u < TWCH; ++u) xc[c0 + u] = y[u];
+            }
+            HB_PC_MARK(13);
         }
         if (CHAIN_I) __syncwarp(); else __syncthreads();
+        HB_PC_MARK(5);
         // P5: inverse radix-RA DFT over k0, untwist, round, wrapping add into the accumulator
         for (int t = SPREAD_I ? ((tid & 31) < RB ? (tid >> 5) * RB + (tid & 31) : G * (K + 1) * RB) : tid; t < G * (K + 1) * RB;
              t += SPREAD_I ? G * (K + 1) * RB : NT) {
@@ -414,7 +464,9 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
             }
         }
         __syncthreads();
+        HB_PC_MARK(6);
     }
+    HB_PC_FLUSH();
 
     // ---- epilogue: sample extract coefficient 0 (App. A.5)
     T* out = reinterpret_cast<T*>(A.out);

@@ -37,3 +37,13 @@ for W in widths:
         t = st["pbs_ms"] + st["ks_ms"]
         best = t if best is None or t < best else best
     print("width %5d: %.3f ms (pbs %.3f ks %.3f)" % (W, best, st["pbs_ms"], st["ks_ms"]))
+    L = E.lib()
+    if hasattr(L, "hb_debug_phase_clocks"):           # -DHB_PHASE_CLOCKS build: critical-path cycles of CTA 0, last launch
+        import ctypes as C
+        buf = (C.c_double * 16)()
+        L.hb_debug_phase_clocks.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        if L.hb_debug_phase_clocks(eng.h, buf) == 0:
+            names = ["P1a", "P1b", "P2+bar", "keywait", "P3+bar", "P4", "P5+bar", "looptop", "P1b:load+twist", "P1b:dft", "P1b:tw+store",
+                     "P4:load", "P4:dft", "P4:tw+store", "-", "-"]
+            n = K.params["n"]
+            print("   cycles/step: " + "  ".join("%s %.0f" % (nm, v / n) for nm, v in zip(names, buf)) + "  total %.0f" % (sum(buf[:8]) / n))
