@@ -292,7 +292,7 @@ hb_status launch_pbs(hb_ctx* c, const void* in, uint32_t in_stride, void* out, u
     a.bsk = (const double2*)c->bsk_f.p; a.wtab = (const double2*)c->wtab.p; a.n = c->p.n; a.base_log = c->p.pbs_base_log;
     // Narrow batches are latency-bound (one bootstrap is n sequential CMUX steps, so what matters is the time of ONE step of
     // ONE CTA).
-    // Measured on boolean default (scripts/narrow_sweep.py, ms per launch): one gate per CTA 2.87 up to 1 x SMs bootstraps;
+    // Measured on boolean default (tests/tools/narrow_sweep.py, ms per launch): one gate per CTA 2.87 up to 1 x SMs bootstraps;
     // two gates per CTA 4.2 up to 2 x SMs; the throughput kernel 6.97 up to 4 x SMs and 10.6 up to 8 x SMs.  So: G = 1 for one
     // wave, G = 2 for at most one wave of pairs, the throughput kernel beyond.  The shortint shapes have no pair instance: G = 1 for one
     // wave (M2C2 6.3 ms, M1C1 2.3 ms), then their wide instances (9.4 / 3.9 ms up to 2 x SMs).  HB_PBS_SMALL=0 disables both, HB_PBS_SMALL_MAX / HB_PBS_SMALL2_MAX override the wave counts.

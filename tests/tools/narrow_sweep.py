@@ -1,10 +1,10 @@
 #!/usr/bin/env python
 """Device time of one boolean level (PBS + KS) against its width, for picking the narrow-batch kernel thresholds
 (engine.cu launch_pbs).  Run on the GPU box; the strategy is chosen with HB_PBS_SMALL / HB_PBS_SMALL_MAX /
-HB_PBS_SMALL2_MAX in the environment.  Scripts may use the oracle for keys (test infrastructure)."""
+HB_PBS_SMALL2_MAX in the environment.  Lives under tests/ because it takes its keys from the oracle (test infrastructure)."""
 import os, sys
 import numpy as np
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "oracle"))
 import helm_b200
 from helm_b200 import engine as E
