@@ -154,6 +154,8 @@ struct Shape {
 template <class Small> constexpr Shape with_small(Shape s) { s.small_smem = &Small::smem; s.small_launch = &Small::launch; return s; }
 template <class Small2> constexpr Shape with_small2(Shape s) { s.small2_smem = &Small2::smem; s.small2_launch = &Small2::launch; return s; }
 
+// pbs_kernel keeps a small static table (untwist factors) beside its dynamic shared memory: 227 KB per CTA minus 1 KB
+constexpr size_t PBS_DYN_SMEM_MAX = 226 * 1024;
 #ifndef HB_SMALL_NT
 #define HB_SMALL_NT 384        // threads of the one-gate boolean instance (288: 100.2 ms, 384: 95.4 ms, 512: 97.9 ms on c7552)
 #endif
@@ -168,7 +170,7 @@ struct Inst {
         auto kern = pbs_kernel<T, N, K, L, RA, RB, G, NT, MINB, STAGE>;
         static bool attr_done = false;
         if (!attr_done) {
-            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PBS_DYN_SMEM_MAX);
             if (e != cudaSuccess) return e;
             attr_done = true;
         }
@@ -303,7 +305,7 @@ hb_status launch_pbs(hb_ctx* c, const void* in, uint32_t in_stride, void* out, u
     const int small_max = small_max_env ? small_max_env : 1;
     if (pair_ok && n_jobs > (uint32_t)(small_max * c->sm_count) && n_jobs <= (uint32_t)(small2_max * c->sm_count)) {
         const size_t sm = sh.small2_smem(c->p.n);
-        if (sm <= 227 * 1024) {
+        if (sm <= PBS_DYN_SMEM_MAX) {
             CU(c, sh.small2_launch(a, c->stream, sm));
             c->stats.kernel_launches++; c->stats.pbs_count += n_jobs;
             return HB_OK;
@@ -311,7 +313,7 @@ hb_status launch_pbs(hb_ctx* c, const void* in, uint32_t in_stride, void* out, u
     }
     if (small_on && sh.small_launch && n_jobs <= (uint32_t)(small_max * c->sm_count)) {
         const size_t sm = sh.small_smem(c->p.n);
-        if (sm <= 227 * 1024) {
+        if (sm <= PBS_DYN_SMEM_MAX) {
             CU(c, sh.small_launch(a, c->stream, sm));
             c->stats.kernel_launches++; c->stats.pbs_count += n_jobs;
             return HB_OK;

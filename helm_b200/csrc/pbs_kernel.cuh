@@ -226,6 +226,16 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
 #ifndef HB_TWCH
 #define HB_TWCH 8
 #endif
+#ifndef HB_SPLIT5
+#define HB_SPLIT5 1
+#endif
+    // inverse-transform tail on all threads: pays for the 32-point split (M2C2 step 14.0 -> 13.0 k cycles), not for 16 x 16
+    constexpr bool SPLIT5 = HB_SPLIT5 && RA >= 32 && G * (K + 1) * RB * 4 <= NT;
+    __shared__ double2 UT[RA];                                          // conj untwist omega^{-RB j1}
+    if (SPLIT5 && threadIdx.x == 0) {
+#pragma unroll
+        for (int j1 = 0; j1 < RA; ++j1) UT[j1] = make_double2(HB_TW_COS[(j1 * C::TWA) & 255], -HB_TW_SIN[(j1 * C::TWA) & 255]);
+    }
     constexpr int TWCH = HB_TWCH < RA && HB_TWCH < RB ? HB_TWCH : (RA < RB ? RA : RB);   // inter-stage twiddles fetched per batch
 #ifndef HB_SPREAD_I
 #define HB_SPREAD_I 1
@@ -449,18 +459,62 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
         for (int t = SPREAD_I ? ((tid & 31) < RB ? (tid >> 5) * RB + (tid & 31) : G * (K + 1) * RB) : tid; t < G * (K + 1) * RB;
              t += SPREAD_I ? G * (K + 1) * RB : NT) {
             const int j0 = t % RB, j = (t / RB) % (K + 1), g = t / (RB * (K + 1));
-            const double2* xr = X + ((size_t)g * ROWS + j) * XROW;
+            double2* xr = X + ((size_t)g * ROWS + j) * XROW;
             double2 x[RA];
 #pragma unroll
             for (int k0 = 0; k0 < RA; ++k0) x[k0] = xr[k0 * (RB + 1) + j0];
+            HB_PC_MARK(14);
             dft_regs<RA, -1>(x);
-            T* ap = acc + ((size_t)g * (K + 1) + j) * N;
+            HB_PC_MARK(15);
+            if (SPLIT5) {                                  // the tail runs on every thread below: leave z in place
 #pragma unroll
-            for (int j1 = 0; j1 < RA; ++j1) {
-                const double2 z = cmul_tw<-1>(x[brev<RA>(j1)], j1 * C::TWA);
-                const int c = j0 + RB * j1;
-                ap[c] += TorusOps<T>::round_add(z.x);
-                ap[c + M] += TorusOps<T>::round_add(z.y);
+                for (int j1 = 0; j1 < RA; ++j1) xr[j1 * (RB + 1) + j0] = x[brev<RA>(j1)];
+                continue;
+            }
+            T* ap = acc + ((size_t)g * (K + 1) + j) * N;
+            // accumulator words are fetched a batch ahead of the stores (same reason as the twiddles in P1b / P4)
+#pragma unroll
+            for (int c0 = 0; c0 < RA; c0 += TWCH) {
+                T lo[TWCH], hi[TWCH];
+#pragma unroll
+                for (int u = 0; u < TWCH; ++u) { lo[u] = ap[j0 + RB * (c0 + u)]; hi[u] = ap[j0 + RB * (c0 + u) + M]; }
+#pragma unroll
+                for (int u = 0; u < TWCH; ++u) {
+                    const double2 z = cmul_tw<-1>(x[brev<RA>(c0 + u)], (c0 + u) * C::TWA);
+                    lo[u] += TorusOps<T>::round_add(z.x);
+                    hi[u] += TorusOps<T>::round_add(z.y);
+                }
+#pragma unroll
+                for (int u = 0; u < TWCH; ++u) { ap[j0 + RB * (c0 + u)] = lo[u]; ap[j0 + RB * (c0 + u) + M] = hi[u]; }
+            }
+        }
+        if (SPLIT5) {
+            // P5b: untwist, round and the wrapping add, spread over all NT threads (the transform above keeps only
+            // G(K+1)RB of them busy; this tail was 2 250 of 14 000 cycles of an M2C2 step on 64 threads)
+            __syncthreads();
+            constexpr int PER = (G * (K + 1) * M + NT - 1) / NT;
+            T lo[PER], hi[PER];
+            double2 z[PER];
+#pragma unroll
+            for (int q = 0; q < PER; ++q) {
+                const int e = tid + q * NT;
+                if (e < G * (K + 1) * M) {
+                    const int pos = e % M, row = e / M, j1 = pos / RB, j0 = pos % RB;   // row = g * (K+1) + j
+                    const double2 v = X[((size_t)(row / (K + 1)) * ROWS + row % (K + 1)) * XROW + j1 * (RB + 1) + j0];
+                    const double2 w = UT[j1];
+                    z[q] = make_double2(fma(v.x, w.x, -(v.y * w.y)), fma(v.x, w.y, v.y * w.x));
+                    const T* ap = acc + (size_t)row * N;
+                    lo[q] = ap[pos]; hi[q] = ap[pos + M];
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < PER; ++q) {
+                const int e = tid + q * NT;
+                if (e < G * (K + 1) * M) {
+                    T* ap = acc + (size_t)(e / M) * N;
+                    ap[e % M] = lo[q] + TorusOps<T>::round_add(z[q].x);
+                    ap[e % M + M] = hi[q] + TorusOps<T>::round_add(z[q].y);
+                }
             }
         }
         __syncthreads();

@@ -44,6 +44,6 @@ for W in widths:
         L.hb_debug_phase_clocks.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         if L.hb_debug_phase_clocks(eng.h, buf) == 0:
             names = ["P1a", "P1b", "P2+bar", "keywait", "P3+bar", "P4", "P5+bar", "looptop", "P1b:load+twist", "P1b:dft", "P1b:tw+store",
-                     "P4:load", "P4:dft", "P4:tw+store", "-", "-"]
+                     "P4:load", "P4:dft", "P4:tw+store", "P5:load", "P5:dft"]
             n = K.params["n"]
             print("   cycles/step: " + "  ".join("%s %.0f" % (nm, v / n) for nm, v in zip(names, buf)) + "  total %.0f" % (sum(buf[:8]) / n))
