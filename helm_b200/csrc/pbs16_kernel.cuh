@@ -184,7 +184,9 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
     }
 
     int a_next = at_own[0];
+    HB_PC_DECL;
     for (int i = 0; i < n; ++i) {
+        HB_PC_MARK(10);
         const int a = a_next;
         a_next = at_own[i + 1];                                         // index n is the body: harmless, never used as a mask
         // A: rotate-subtract and signed decomposition of this thread's 32 coefficients c = idx + 16 m, all L levels.
@@ -223,6 +225,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
                 }
             }
         }
+        HB_PC_MARK(0);
         double2 o1[PP][G][K + 1];
         double2 o2[I2 > 0 ? I2 : 1][G];
 #pragma unroll
@@ -260,12 +263,14 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
 #pragma unroll
                     for (int k0 = 0; k0 < R; ++k0) y[k0] = cmul(x[brev<R>(k0)], W[k0 * (R + 1) + idx]);
                 }
+                HB_PC_MARK(1);
                 // ... then wait until every thread has consumed the previous level's spectra, and publish the row
                 if (lev > 0) { mbar_wait(mbar, parity); parity ^= 1u; }
 #pragma unroll
                 for (int k0 = 0; k0 < R; ++k0) xr[k0 * (R + 1) + idx] = y[k0];
             }
             __syncwarp();
+            HB_PC_MARK(2);
             // C: radix-16 DFT over j0 of column k0 = idx, in place
             {
                 double2* xc = xr + idx * (R + 1);
@@ -276,6 +281,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
 #pragma unroll
                 for (int k1 = 0; k1 < R; ++k1) xc[k1] = x[brev<R>(k1)];
             }
+            HB_PC_MARK(3);
             // D: pointwise MAC of this level's (K+1) spectra per gate with rows lev*(K+1)+r of BSK_i, one group of
             // (whole position, left-over item) at a time.  The key loads do not depend on the spectra: the first group's
             // are issued before the barrier.
@@ -298,6 +304,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
             };
             load_group(0);
             __syncthreads();
+            HB_PC_MARK(4);
 #pragma unroll
             for (int q = 0; q < NGRP; ++q) {
                 if (q > 0) load_group(q);
@@ -322,6 +329,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
                     }
                 }
             }
+            HB_PC_MARK(5);
             mbar_arrive(mbar);                       // this thread no longer reads this level's spectra
 #pragma unroll
             for (int l = 0; l + 1 < L; ++l)
@@ -329,7 +337,9 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
                 for (int part = 0; part < R / 2; ++part) pk[l][part] = pk[l + 1][part];
         }
         // output spectra -> the buffers of the polynomials they belong to (once everyone is done reading them)
+        HB_PC_MARK(11);
         mbar_wait(mbar, parity); parity ^= 1u;
+        HB_PC_MARK(6);
 #pragma unroll
         for (int q = 0; q < PP; ++q) {
             const int s1 = spos(NT >= M ? tid : tid + q * NT);
@@ -345,6 +355,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
             for (int g = 0; g < G; ++g) X[((size_t)g * (K + 1) + j2) * XROW + s2] = o2[q][g];
         }
         __syncthreads();
+        HB_PC_MARK(7);
         // E: inverse radix-16 DFT over k1 of column k0 = idx, conj inter-stage twiddle
         {
             double2* xc = xr + idx * (R + 1);
@@ -366,6 +377,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
             }
         }
         __syncwarp();
+        HB_PC_MARK(8);
         // F: inverse radix-16 DFT over k0, untwist, round, wrapping add into the accumulator
         {
             double2 x[R];
@@ -383,7 +395,9 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
             }
         }
         __syncwarp();
+        HB_PC_MARK(9);
     }
+    HB_PC_FLUSH();
     __syncthreads();
 
     // ---- epilogue: sample extract coefficient 0 (App. A.5)

@@ -46,4 +46,6 @@ for W in widths:
             names = ["P1a", "P1b", "P2+bar", "keywait", "P3+bar", "P4", "P5+bar", "looptop", "P1b:load+twist", "P1b:dft", "P1b:tw+store",
                      "P4:load", "P4:dft", "P4:tw+store", "P5:load", "P5:dft"]
             n = K.params["n"]
+            if os.environ.get("SWEEP_PBS16"):
+                names = ["A", "B", "wait+store", "C", "load+bar", "D", "lastwait", "O+bar", "E", "F", "top", "rotate-pk", "-", "-", "-", "-"]
             print("   cycles/step: " + "  ".join("%s %.0f" % (nm, v / n) for nm, v in zip(names, buf)) + "  total %.0f" % (sum(buf[:8]) / n))
