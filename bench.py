@@ -331,16 +331,21 @@ def main():
 
     fp64_peak = eng.fp64_peak_tflops()
 
-    # ---- device-resident timing
+    # ---- device-resident timing.  The clock sampler starts before the warm-up: nvidia-smi's start-up (NVML attach) stalls
+    # driver calls for tens of ms, which landed inside the timed region when it was started after the barrier
+    # (ms_per_step 576 .. 599 for the same 575 ms of kernels); its samples cover warm-up + timed steps, the same load
+    clk = Clocks(local) if rank == 0 else None
     for s in range(args.warmup):
         step_resident(s)
     barrier()
     st0 = eng.stats()
-    clk = Clocks(local) if rank == 0 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(ext)
+    enqueue_ms = []                                  # host time of each step's enqueue (job build + upload + launches)
     for s in range(args.warmup, args.warmup + args.steps):
+        th = time.perf_counter()
         step_resident(s)
+        enqueue_ms.append(round(1e3 * (time.perf_counter() - th), 3))
     e1.record(ext)
     barrier()
     clocks = clk.stop() if clk else None
@@ -455,7 +460,7 @@ def main():
                                                "Fourier key stays in L2, DRAM traffic is ~22 GB/s)",
                              "peak_source": "measured in this run: register-resident DFMA loop (hb_measure_fp64_peak); "
                                             "MEASURED_PEAKS.json has no FP64 entry",
-                             "flops_per_launch": flops_per_launch, "kernel_ms": pbs_ms, "ks_kernel_ms": ks_ms, "gap_ms": gap_ms,
+                             "flops_per_launch": flops_per_launch, "kernel_ms": pbs_ms, "ks_kernel_ms": ks_ms, "gap_ms": gap_ms, "host_enqueue_ms": enqueue_ms,
                              "hbm_floor_ms": 1e3 * (bsk_bytes + 3.0 * Wr * words * 4) / (hbm_peak_gbs() * 1e9)},
                 "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
                 "verified": verified, "c7552_gates_mode": c7552, "c7552_lut_mode": c7552_lut}

@@ -99,6 +99,14 @@ template <class T> __global__ void gather_rows(const T* src, uint32_t stride, T*
         for (uint32_t x = blockIdx.x * blockDim.x + threadIdx.x; x < words; x += gridDim.x * blockDim.x) d[x] = s[x];
     }
 }
+// packed rows (words each) <-> strided rows, contiguous range: the device side of a large host copy, so that the PCIe transfer
+// itself is one 1-D copy (a 2-D copy of 2.9 KB rows reaches about half the link rate)
+template <class T> __global__ void repack_rows(T* dst, uint32_t dstride, const T* src, uint32_t sstride, uint32_t cnt, uint32_t words) {
+    for (uint32_t r = blockIdx.y; r < cnt; r += gridDim.y) {
+        T* d = dst + (size_t)r * dstride; const T* q = src + (size_t)r * sstride;
+        for (uint32_t x = blockIdx.x * blockDim.x + threadIdx.x; x < words; x += gridDim.x * blockDim.x) d[x] = q[x];
+    }
+}
 struct LinJob { uint32_t src, dst; int32_t c; uint32_t pad; uint64_t cst; };   // dst = c*src + cst(body); c==0: trivial
 template <class T> __global__ void linear_rows(T* w, uint32_t stride, const LinJob* jobs, uint32_t cnt, uint32_t words) {
     for (uint32_t r = blockIdx.y; r < cnt; r += gridDim.y) {
@@ -272,8 +280,16 @@ hb_status upload_jobs(hb_ctx* c, const std::vector<PbsJob>& pj, const std::vecto
     fold_timing(c, s, &ex->slots[ex->next % NSLOT]);
     const size_t a = pj.size() * sizeof(PbsJob), b = kj.size() * sizeof(KsJob), d = lj.size() * sizeof(LinJob);
     const size_t oa = 0, ob = (a + 15) & ~(size_t)15, od = ob + ((b + 15) & ~(size_t)15), tot = od + d + 16;
-    CU(c, s.pin.ensure(tot));
-    CU(c, s.dev.ensure(tot));
+    if (s.pin.cap < tot || s.dev.cap < tot) {
+        // grow every slot of the ring at once: otherwise the pinned / device allocations of slots 1 .. NSLOT-1 (tens of ms
+        // each on a busy host) land in the second .. fourth batch, i.e. inside a caller's timed region after a short warm-up
+        for (JobSlot& o : ex->slots) {
+            if (o.pin.cap >= tot && o.dev.cap >= tot) continue;
+            if (&o != &s && o.done) CU(c, cudaEventSynchronize(o.done));
+            CU(c, o.pin.ensure(tot));
+            CU(c, o.dev.ensure(tot));
+        }
+    }
     char* h = (char*)s.pin.p;
     if (a) memcpy(h + oa, pj.data(), a);
     if (b) memcpy(h + ob, kj.data(), b);
@@ -580,6 +596,7 @@ hb_status hb_wires_read(hb_wires* w, const uint32_t* idx, uint32_t cnt, void* ho
     return HB_OK;
 }
 
+static constexpr size_t BIG_COPY = 4u << 20;   // row-range copies from this size go through a 1-D transfer + device repack
 hb_status hb_wires_write_rows(hb_wires* w, uint32_t first, uint32_t cnt, const void* host) {
     if (!w || (!host && cnt)) return HB_ERR_ARG;
     if (!cnt) return HB_OK;
@@ -587,7 +604,18 @@ hb_status hb_wires_write_rows(hb_wires* w, uint32_t first, uint32_t cnt, const v
     if ((uint64_t)first + cnt > w->n_wires) return fail(c, HB_ERR_ARG, "wire row range out of bounds");
     CU(c, cudaSetDevice(c->device));
     const size_t ts = tsize(c), words = ct_words(c), stride = hb_wire_stride(c);
-    CU(c, cudaMemcpy2DAsync((char*)w->dev + (size_t)first * stride * ts, stride * ts, host, words * ts, words * ts, cnt, cudaMemcpyHostToDevice, c->stream));
+    char* drow = (char*)w->dev + (size_t)first * stride * ts;
+    if ((size_t)cnt * words * ts >= BIG_COPY) {
+        CU(c, c->stage_dev.ensure((size_t)cnt * words * ts));
+        CU(c, cudaMemcpyAsync(c->stage_dev.p, host, (size_t)cnt * words * ts, cudaMemcpyHostToDevice, c->stream));
+        const dim3 grid((unsigned)((words + 255) / 256), cnt < 65535 ? cnt : 65535);
+        if (ts == 4) repack_rows<uint32_t><<<grid, 256, 0, c->stream>>>((uint32_t*)drow, (uint32_t)stride, (const uint32_t*)c->stage_dev.p, (uint32_t)words, cnt, (uint32_t)words);
+        else repack_rows<uint64_t><<<grid, 256, 0, c->stream>>>((uint64_t*)drow, (uint32_t)stride, (const uint64_t*)c->stage_dev.p, (uint32_t)words, cnt, (uint32_t)words);
+        CU(c, cudaGetLastError());
+        c->stats.kernel_launches++;
+    } else {
+        CU(c, cudaMemcpy2DAsync(drow, stride * ts, host, words * ts, words * ts, cnt, cudaMemcpyHostToDevice, c->stream));
+    }
     CU(c, cudaStreamSynchronize(c->stream));
     return HB_OK;
 }
@@ -598,7 +626,18 @@ hb_status hb_wires_read_rows(hb_wires* w, uint32_t first, uint32_t cnt, void* ho
     if ((uint64_t)first + cnt > w->n_wires) return fail(c, HB_ERR_ARG, "wire row range out of bounds");
     CU(c, cudaSetDevice(c->device));
     const size_t ts = tsize(c), words = ct_words(c), stride = hb_wire_stride(c);
-    CU(c, cudaMemcpy2DAsync(host, words * ts, (const char*)w->dev + (size_t)first * stride * ts, stride * ts, words * ts, cnt, cudaMemcpyDeviceToHost, c->stream));
+    const char* drow = (const char*)w->dev + (size_t)first * stride * ts;
+    if ((size_t)cnt * words * ts >= BIG_COPY) {
+        CU(c, c->stage_dev.ensure((size_t)cnt * words * ts));
+        const dim3 grid((unsigned)((words + 255) / 256), cnt < 65535 ? cnt : 65535);
+        if (ts == 4) repack_rows<uint32_t><<<grid, 256, 0, c->stream>>>((uint32_t*)c->stage_dev.p, (uint32_t)words, (const uint32_t*)drow, (uint32_t)stride, cnt, (uint32_t)words);
+        else repack_rows<uint64_t><<<grid, 256, 0, c->stream>>>((uint64_t*)c->stage_dev.p, (uint32_t)words, (const uint64_t*)drow, (uint32_t)stride, cnt, (uint32_t)words);
+        CU(c, cudaGetLastError());
+        c->stats.kernel_launches++;
+        CU(c, cudaMemcpyAsync(host, c->stage_dev.p, (size_t)cnt * words * ts, cudaMemcpyDeviceToHost, c->stream));
+    } else {
+        CU(c, cudaMemcpy2DAsync(host, words * ts, drow, stride * ts, words * ts, cnt, cudaMemcpyDeviceToHost, c->stream));
+    }
     CU(c, cudaStreamSynchronize(c->stream));
     return HB_OK;
 }
