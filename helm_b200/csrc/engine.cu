@@ -17,6 +17,7 @@
 #define HB_PBS16_G 4
 #endif
 #include "ks_kernel.cuh"
+#include "ks_mma_kernel.cuh"
 
 using namespace hb;
 
@@ -59,6 +60,7 @@ struct hb_ctx {
     bool have_params = false, have_bsk = false, have_ksk = false;
     int shape = -1;                        // index into the kernel shape table
     DevBuf bsk_f, ksk, wtab;               // resident keys
+    DevBuf ksk_planes; int ksk_npad = 0;   // byte planes of the KSK for the tensor-core keyswitch (u32, ks_level 4)
     DevBuf scratch_a, scratch_b;           // PBS->KS (order 0) or KS->PBS (order 1) intermediates
     DevBuf atil;                           // switched masks of the running PBS batch (pbs16_kernel)
     DevBuf jobs_dev, stage_dev, idx_dev;
@@ -350,6 +352,21 @@ hb_status launch_ks(hb_ctx* c, const void* in, uint32_t in_stride, void* out, ui
     KsArgs a;
     a.in = in; a.in_stride = in_stride; a.out = out; a.out_stride = out_stride; a.jobs = jobs; a.n_jobs = n_jobs;
     a.ksk = c->ksk.p; a.n = c->p.n; a.kN = c->p.k * c->p.N; a.base_log = c->p.ks_base_log; a.level = c->p.ks_level;
+    // wide batches on the tensor cores (bit-identical; HB_KS_MMA=0 keeps the IMAD kernel)
+    static const int mma_on = getenv("HB_KS_MMA") ? atoi(getenv("HB_KS_MMA")) : 1;
+    static const int mma_min = getenv("HB_KS_MMA_MIN") ? atoi(getenv("HB_KS_MMA_MIN")) : 2048;
+    if (mma_on && c->ksk_npad && n_jobs >= (uint32_t)mma_min) {
+        KsMmaArgs m;
+        m.a = a; m.a.split = 1; m.planes = (const uint8_t*)c->ksk_planes.p; m.npad = c->ksk_npad;
+        static bool attr_done = false;
+        const size_t smem = (size_t)(KM_TM + 4 * KM_TN) * KM_PITCH;
+        if (!attr_done) { CU(c, cudaFuncSetAttribute(ks_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_done = true; }
+        const dim3 grid((n_jobs + KM_TM - 1) / KM_TM, c->ksk_npad / KM_TN);
+        ks_mma_kernel<<<grid, KM_NT, smem, c->stream>>>(m);
+        CU(c, cudaGetLastError());
+        c->stats.kernel_launches++; c->stats.ks_count += n_jobs;
+        return HB_OK;
+    }
     const unsigned tiles = (n_jobs + KS_TB - 1) / KS_TB;
     // narrow batches: fewer tiles than SMs would leave each CTA streaming the whole key alone -- split the mask
     // dimension over gridDim.y CTAs (partial sums added atomically; wrapping integer adds, so still bit-exact)
@@ -432,7 +449,7 @@ hb_status hb_ctx_destroy(hb_ctx* c) {
     if (!c) return HB_ERR_ARG;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    for (DevBuf* b : {&c->bsk_f, &c->ksk, &c->wtab, &c->scratch_a, &c->scratch_b, &c->atil, &c->jobs_dev, &c->stage_dev, &c->idx_dev}) b->release();
+    for (DevBuf* b : {&c->bsk_f, &c->ksk, &c->ksk_planes, &c->wtab, &c->scratch_a, &c->scratch_b, &c->atil, &c->jobs_dev, &c->stage_dev, &c->idx_dev}) b->release();
     c->jobs_pin.release(); c->stage_pin.release();
     for (size_t i = 0; i < g_extra.size(); ++i)
         if (g_extra[i].first == c) {
@@ -502,6 +519,14 @@ hb_status hb_load_ksk(hb_ctx* c, const void* ksk, size_t bytes) {
     if (bytes != want) return fail(c, HB_ERR_ARG, "hb_load_ksk: byte size does not match [kN][l_ks][n+1]");
     CU(c, c->ksk.ensure(want));
     CU(c, cudaMemcpyAsync(c->ksk.p, ksk, want, cudaMemcpyHostToDevice, c->stream));
+    c->ksk_npad = 0;
+    if (p.torus_bits == 32 && p.ks_level == KM_L && (p.k * p.N) % 32 == 0 && p.ks_base_log <= 7) {   // ks_mma_kernel.cuh
+        const int K = p.k * p.N * KM_L, npad = ((p.n + 1 + KM_TN - 1) / KM_TN) * KM_TN;
+        CU(c, c->ksk_planes.ensure((size_t)4 * npad * K));
+        ksk_planes_kernel<<<4 * c->sm_count, 256, 0, c->stream>>>((const uint32_t*)c->ksk.p, (uint8_t*)c->ksk_planes.p, p.n, K, npad);
+        CU(c, cudaGetLastError());
+        c->ksk_npad = npad;
+    }
     CU(c, cudaStreamSynchronize(c->stream));
     c->have_ksk = true;
     return HB_OK;

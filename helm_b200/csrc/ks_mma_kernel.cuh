@@ -1,0 +1,163 @@
+// Wide-batch LWE keyswitch on the tensor cores (u32 torus, ks_level = 4), same contract as ks_kernel.cuh:
+//   out = (0,...,0,b_in) - sum_i sum_l d_{i,l} * KSK[i][l]     (wrapping mod 2^32, digits in [-B/2, B/2])
+// For a level of W gates this is a dense integer contraction [W x kN*l] . [kN*l x (n+1)] (W = 65 536: 194 G multiply-adds),
+// 3.2 % of the level in the IMAD form.  Here the 32-bit key words are split once, at hb_load_ksk, into four unsigned byte
+// planes, the signed digits are int8, and every plane is accumulated exactly in int32 by mma.sync m16n8k32 (s8 x u8):
+// |sum| <= kN*l * 128 * 255 < 2^31.  The planes are recombined with shifts, which wrap exactly like the 32-bit product, so
+// the result is bit-identical to ks_kernel's.  (mma.sync, not tcgen05: the operand A -- the digits -- is produced in the
+// kernel from the bootstrap outputs, and the whole keyswitch is ~3 % of the step; the legacy path already makes it ~1 %.)
+//
+// CTA = 64 gates x 64 output columns, 8 warps as 4 (gates) x 2 (columns), warp tile 16 x 32 x 4 planes = 64 accumulator
+// registers.  K = kN*l is walked in chunks of 128: the key chunk [4 planes][64 cols][128 B] arrives by cp.async while the
+// threads decompose the chunk's 32 mask words of the 64 gates (linear part of the job fused, as in ks_kernel) into the
+// A tile [64][128 B].  Rows are padded to 144 B so that fragment loads are bank-conflict free.
+#pragma once
+#include "ks_kernel.cuh"
+
+namespace hb {
+
+constexpr int KM_TM = 64, KM_TN = 64, KM_KC = 128, KM_NT = 256, KM_PITCH = 144, KM_L = 4;
+
+struct KsMmaArgs {
+    KsArgs a;
+    const uint8_t* planes;     // [4][npad][K] bytes, K = kN * 4, k = i * 4 + level
+    int32_t npad;              // columns padded to a multiple of KM_TN (zero filled)
+};
+
+// KSK [kN][l][n+1] u32 -> byte planes [4][npad][K]
+__global__ void ksk_planes_kernel(const uint32_t* ksk, uint8_t* planes, int n, int K, int npad) {
+    const size_t total = (size_t)npad * K;
+    for (size_t x = (size_t)blockIdx.x * blockDim.x + threadIdx.x; x < total; x += (size_t)gridDim.x * blockDim.x) {
+        const int k = (int)(x % K), col = (int)(x / K);
+        const uint32_t w = col <= n ? ksk[(size_t)k * (n + 1) + col] : 0u;
+#pragma unroll
+        for (int p = 0; p < 4; ++p) planes[((size_t)p * npad + col) * K + k] = (uint8_t)(w >> (8 * p));
+    }
+}
+
+__device__ __forceinline__ void mma_s8u8(int (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+
+__global__ void __launch_bounds__(KM_NT, 2) ks_mma_kernel(const KsMmaArgs P) {
+    const KsArgs& A = P.a;
+    extern __shared__ __align__(16) unsigned char km_smem[];
+    unsigned char* As = km_smem;                                       // [64][144]
+    unsigned char* Bs = km_smem + KM_TM * KM_PITCH;                    // [4][64][144]
+    __shared__ KsJob jobs[KM_TM];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n = A.n, kN = A.kN, BL = A.base_log, K = kN * KM_L;
+    const int job0 = blockIdx.x * KM_TM, col0 = blockIdx.y * KM_TN;
+    const int njob = min(KM_TM, (int)A.n_jobs - job0);
+    if (tid < KM_TM) {
+        KsJob j = {{0, 0, 0, 0}, {0, 0, 0, 0}, 0, 0, 0};
+        if (tid < njob) j = A.jobs[job0 + tid];
+        jobs[tid] = j;
+    }
+    __syncthreads();
+    const uint32_t* in = reinterpret_cast<const uint32_t*>(A.in);
+    const int wm = warp & 3, wn = warp >> 2;                           // warp tile: gates 16 wm .., columns 32 wn ..
+    int acc[4][4][4];                                                  // [n block][plane][fragment register]
+#pragma unroll
+    for (int nb = 0; nb < 4; ++nb)
+#pragma unroll
+        for (int p = 0; p < 4; ++p)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) acc[nb][p][e] = 0;
+
+    const int tot = BL * KM_L;
+    const uint32_t mask = (1u << BL) - 1;
+    const uint32_t bs_addr = (uint32_t)__cvta_generic_to_shared(Bs);
+    for (int k0 = 0; k0 < K; k0 += KM_KC) {
+        // key chunk: 4 planes x 64 columns x 128 bytes, 16 bytes per cp.async
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            const int q = tid + r * KM_NT, p = q >> 9, col = (q >> 3) & 63, part = q & 7;
+            cp_async16(bs_addr + (uint32_t)((p * KM_TN + col) * KM_PITCH + part * 16),
+                       P.planes + ((size_t)p * P.npad + col0 + col) * K + k0 + part * 16);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        // digits of mask words i0 .. i0+31 for the 64 gates (tfhe-rs SignedDecomposer, App. A.3): lane = word, warp = 8 gates
+        const int i = (k0 >> 2) + lane;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            const int g = warp * 8 + r;
+            uint32_t v = 0;
+            if (g < njob) {
+                const KsJob& j = jobs[g];
+#pragma unroll
+                for (int s = 0; s < 4; ++s)
+                    if (j.c[s]) v += (uint32_t)j.c[s] * in[(size_t)j.src[s] * A.in_stride + i];
+            }
+            uint32_t state = v;
+            if (tot < 32) {
+                state = v >> (32 - tot - 1);
+                state = (state + 1) >> 1;
+                state &= (1u << tot) - 1;
+            }
+            uint32_t packed = 0;
+#pragma unroll
+            for (int l = KM_L - 1; l >= 0; --l) {
+                uint32_t res = state & mask;
+                state >>= BL;
+                uint32_t carry = ((res - 1) | state) & res;
+                carry >>= (BL - 1);
+                state += carry;
+                packed |= (uint32_t)(uint8_t)(int8_t)((int32_t)res - (int32_t)(carry << BL)) << (8 * l);
+            }
+            *reinterpret_cast<uint32_t*>(As + g * KM_PITCH + lane * 4) = packed;
+        }
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncthreads();
+#pragma unroll
+        for (int ks = 0; ks < KM_KC / 32; ++ks) {
+            uint32_t a[4];
+            const unsigned char* ap = As + (wm * 16 + (lane >> 2)) * KM_PITCH + ks * 32 + (lane & 3) * 4;
+            a[0] = *reinterpret_cast<const uint32_t*>(ap);
+            a[1] = *reinterpret_cast<const uint32_t*>(ap + 8 * KM_PITCH);
+            a[2] = *reinterpret_cast<const uint32_t*>(ap + 16);
+            a[3] = *reinterpret_cast<const uint32_t*>(ap + 8 * KM_PITCH + 16);
+#pragma unroll
+            for (int p = 0; p < 4; ++p)
+#pragma unroll
+                for (int nb = 0; nb < 4; ++nb) {
+                    const unsigned char* bp = Bs + (p * KM_TN + wn * 32 + nb * 8 + (lane >> 2)) * KM_PITCH + ks * 32 + (lane & 3) * 4;
+                    mma_s8u8(acc[nb][p], a, *reinterpret_cast<const uint32_t*>(bp), *reinterpret_cast<const uint32_t*>(bp + 16));
+                }
+        }
+        __syncthreads();
+    }
+    // out = (0, ..., 0, body) - sum: fragment rows lane/4 and lane/4 + 8, columns 2 (lane%4) and + 1
+    uint32_t* out = reinterpret_cast<uint32_t*>(A.out);
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int g = wm * 16 + (lane >> 2) + 8 * h;
+        if (g >= njob) continue;
+        const KsJob& j = jobs[g];
+        uint32_t* o = out + (size_t)j.dst * A.out_stride;
+#pragma unroll
+        for (int nb = 0; nb < 4; ++nb)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int c = col0 + wn * 32 + nb * 8 + (lane & 3) * 2 + e;
+                if (c > n) continue;
+                const uint32_t sum = (uint32_t)acc[nb][0][2 * h + e] + ((uint32_t)acc[nb][1][2 * h + e] << 8) +
+                                     ((uint32_t)acc[nb][2][2 * h + e] << 16) + ((uint32_t)acc[nb][3][2 * h + e] << 24);
+                uint32_t v = 0;
+                if (c == n) {
+#pragma unroll
+                    for (int s = 0; s < 4; ++s)
+                        if (j.c[s]) v += (uint32_t)j.c[s] * in[(size_t)j.src[s] * A.in_stride + kN];
+                    v += (uint32_t)j.cst;
+                }
+                o[c] = v - sum;
+            }
+    }
+}
+
+}  // namespace hb
