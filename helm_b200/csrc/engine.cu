@@ -60,7 +60,7 @@ struct hb_ctx {
     bool have_params = false, have_bsk = false, have_ksk = false;
     int shape = -1;                        // index into the kernel shape table
     DevBuf bsk_f, ksk, wtab;               // resident keys
-    DevBuf ksk_planes; int ksk_npad = 0;   // byte planes of the KSK for the tensor-core keyswitch (u32, ks_level 4)
+    DevBuf ksk_planes, ks_dig; int ksk_npad = 0;   // byte planes of the KSK for the tensor-core keyswitch (u32, ks_level 4)
     DevBuf scratch_a, scratch_b;           // PBS->KS (order 0) or KS->PBS (order 1) intermediates
     DevBuf atil;                           // switched masks of the running PBS batch (pbs16_kernel)
     DevBuf jobs_dev, stage_dev, idx_dev;
@@ -352,18 +352,22 @@ hb_status launch_ks(hb_ctx* c, const void* in, uint32_t in_stride, void* out, ui
     KsArgs a;
     a.in = in; a.in_stride = in_stride; a.out = out; a.out_stride = out_stride; a.jobs = jobs; a.n_jobs = n_jobs;
     a.ksk = c->ksk.p; a.n = c->p.n; a.kN = c->p.k * c->p.N; a.base_log = c->p.ks_base_log; a.level = c->p.ks_level;
-    // wide batches on the tensor cores (bit-identical; HB_KS_MMA=0 keeps the IMAD kernel)
+    // batches from ~100 jobs on the tensor cores (bit-identical; HB_KS_MMA=0 keeps the IMAD kernel)
     static const int mma_on = getenv("HB_KS_MMA") ? atoi(getenv("HB_KS_MMA")) : 1;
-    static const int mma_min = getenv("HB_KS_MMA_MIN") ? atoi(getenv("HB_KS_MMA_MIN")) : 2048;
+    static const int mma_min = getenv("HB_KS_MMA_MIN") ? atoi(getenv("HB_KS_MMA_MIN")) : 96;   // tests/tools/narrow_sweep.py: 0.050 ms up to 592 jobs, IMAD 0.044 (64) .. 0.195 (592)
     if (mma_on && c->ksk_npad && n_jobs >= (uint32_t)mma_min) {
         KsMmaArgs m;
         m.a = a; m.a.split = 1; m.planes = (const uint8_t*)c->ksk_planes.p; m.npad = c->ksk_npad;
-        static bool attr_done = false;
-        const size_t smem = (size_t)(KM_TM + 4 * KM_TN) * KM_PITCH;
-        if (!attr_done) { CU(c, cudaFuncSetAttribute(ks_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_done = true; }
         const dim3 grid((n_jobs + KM_TM - 1) / KM_TM, c->ksk_npad / KM_TN);
-        ks_mma_kernel<<<grid, KM_NT, smem, c->stream>>>(m);
+        const uint32_t rows_pad = grid.x * KM_TM;
+        CU(c, c->ks_dig.ensure((size_t)rows_pad * a.kN * KM_L));
+        ks_digits_kernel<<<rows_pad < 65535u ? rows_pad : 65535u, 256, 0, c->stream>>>(m.a, (uint8_t*)c->ks_dig.p, rows_pad);
+        static bool attr2 = false;
+        const size_t smem2 = 2 * (size_t)KM_STAGE;
+        if (!attr2) { CU(c, cudaFuncSetAttribute(ks_mma2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2)); attr2 = true; }
+        ks_mma2_kernel<<<grid, KM_NT, smem2, c->stream>>>(m, (const uint8_t*)c->ks_dig.p);
         CU(c, cudaGetLastError());
+        c->stats.kernel_launches++;
         c->stats.kernel_launches++; c->stats.ks_count += n_jobs;
         return HB_OK;
     }
@@ -449,7 +453,7 @@ hb_status hb_ctx_destroy(hb_ctx* c) {
     if (!c) return HB_ERR_ARG;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    for (DevBuf* b : {&c->bsk_f, &c->ksk, &c->ksk_planes, &c->wtab, &c->scratch_a, &c->scratch_b, &c->atil, &c->jobs_dev, &c->stage_dev, &c->idx_dev}) b->release();
+    for (DevBuf* b : {&c->bsk_f, &c->ksk, &c->ksk_planes, &c->ks_dig, &c->wtab, &c->scratch_a, &c->scratch_b, &c->atil, &c->jobs_dev, &c->stage_dev, &c->idx_dev}) b->release();
     c->jobs_pin.release(); c->stage_pin.release();
     for (size_t i = 0; i < g_extra.size(); ++i)
         if (g_extra[i].first == c) {

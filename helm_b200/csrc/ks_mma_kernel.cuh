@@ -4,13 +4,14 @@
 // 3.2 % of the level in the IMAD form.  Here the 32-bit key words are split once, at hb_load_ksk, into four unsigned byte
 // planes, the signed digits are int8, and every plane is accumulated exactly in int32 by mma.sync m16n8k32 (s8 x u8):
 // |sum| <= kN*l * 128 * 255 < 2^31.  The planes are recombined with shifts, which wrap exactly like the 32-bit product, so
-// the result is bit-identical to ks_kernel's.  (mma.sync, not tcgen05: the operand A -- the digits -- is produced in the
-// kernel from the bootstrap outputs, and the whole keyswitch is ~3 % of the step; the legacy path already makes it ~1 %.)
+// the result is bit-identical to ks_kernel's.  (mma.sync, not tcgen05: the keyswitch was 3.2 % of the step and the legacy
+// tensor path already brings it to 0.6 %: 18.7 -> 3.2 ms per 64k-gate level.)
 //
-// CTA = 64 gates x 64 output columns, 8 warps as 4 (gates) x 2 (columns), warp tile 16 x 32 x 4 planes = 64 accumulator
-// registers.  K = kN*l is walked in chunks of 128: the key chunk [4 planes][64 cols][128 B] arrives by cp.async while the
-// threads decompose the chunk's 32 mask words of the 64 gates (linear part of the job fused, as in ks_kernel) into the
-// A tile [64][128 B].  Rows are padded to 144 B so that fragment loads are bank-conflict free.
+// ks_digits_kernel writes the digits once to a scratch array [gates][K] (int8; the job's linear part fused, as in
+// ks_kernel).  ks_mma2_kernel: CTA = 64 gates x 64 output columns, 8 warps as 4 (gates) x 2 (columns), warp tile
+// 16 x 32 x 4 planes = 64 accumulator registers; K = kN*l is walked in chunks of 128 through a two-stage cp.async ring
+// (A tile [64][128 B] + key tile [4 planes][64 cols][128 B] per stage, 2 CTAs per SM).  Rows are padded to 144 B so that
+// the fragment loads are bank-conflict free.
 #pragma once
 #include "ks_kernel.cuh"
 
@@ -44,56 +45,20 @@ __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
 }
 
-__global__ void __launch_bounds__(KM_NT, 2) ks_mma_kernel(const KsMmaArgs P) {
-    const KsArgs& A = P.a;
-    extern __shared__ __align__(16) unsigned char km_smem[];
-    unsigned char* As = km_smem;                                       // [64][144]
-    unsigned char* Bs = km_smem + KM_TM * KM_PITCH;                    // [4][64][144]
-    __shared__ KsJob jobs[KM_TM];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int n = A.n, kN = A.kN, BL = A.base_log, K = kN * KM_L;
-    const int job0 = blockIdx.x * KM_TM, col0 = blockIdx.y * KM_TN;
-    const int njob = min(KM_TM, (int)A.n_jobs - job0);
-    if (tid < KM_TM) {
-        KsJob j = {{0, 0, 0, 0}, {0, 0, 0, 0}, 0, 0, 0};
-        if (tid < njob) j = A.jobs[job0 + tid];
-        jobs[tid] = j;
-    }
-    __syncthreads();
-    const uint32_t* in = reinterpret_cast<const uint32_t*>(A.in);
-    const int wm = warp & 3, wn = warp >> 2;                           // warp tile: gates 16 wm .., columns 32 wn ..
-    int acc[4][4][4];                                                  // [n block][plane][fragment register]
-#pragma unroll
-    for (int nb = 0; nb < 4; ++nb)
-#pragma unroll
-        for (int p = 0; p < 4; ++p)
-#pragma unroll
-            for (int e = 0; e < 4; ++e) acc[nb][p][e] = 0;
-
-    const int tot = BL * KM_L;
+// digits of every mask word of every job, tfhe-rs SignedDecomposer (App. A.3); rows beyond n_jobs are zero
+__global__ void __launch_bounds__(256) ks_digits_kernel(const KsArgs A, uint8_t* dig, uint32_t rows_pad) {
+    const int kN = A.kN, BL = A.base_log, tot = BL * KM_L;
     const uint32_t mask = (1u << BL) - 1;
-    const uint32_t bs_addr = (uint32_t)__cvta_generic_to_shared(Bs);
-    for (int k0 = 0; k0 < K; k0 += KM_KC) {
-        // key chunk: 4 planes x 64 columns x 128 bytes, 16 bytes per cp.async
-#pragma unroll
-        for (int r = 0; r < 8; ++r) {
-            const int q = tid + r * KM_NT, p = q >> 9, col = (q >> 3) & 63, part = q & 7;
-            cp_async16(bs_addr + (uint32_t)((p * KM_TN + col) * KM_PITCH + part * 16),
-                       P.planes + ((size_t)p * P.npad + col0 + col) * K + k0 + part * 16);
-        }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-        // digits of mask words i0 .. i0+31 for the 64 gates (tfhe-rs SignedDecomposer, App. A.3): lane = word, warp = 8 gates
-        const int i = (k0 >> 2) + lane;
-#pragma unroll
-        for (int r = 0; r < 8; ++r) {
-            const int g = warp * 8 + r;
+    const uint32_t* in = reinterpret_cast<const uint32_t*>(A.in);
+    for (uint32_t g = blockIdx.x; g < rows_pad; g += gridDim.x) {
+        KsJob j = {{0, 0, 0, 0}, {0, 0, 0, 0}, 0, 0, 0};
+        if (g < A.n_jobs) j = A.jobs[g];
+        uint32_t* row = reinterpret_cast<uint32_t*>(dig + (size_t)g * kN * KM_L);
+        for (int i = threadIdx.x; i < kN; i += blockDim.x) {
             uint32_t v = 0;
-            if (g < njob) {
-                const KsJob& j = jobs[g];
 #pragma unroll
-                for (int s = 0; s < 4; ++s)
-                    if (j.c[s]) v += (uint32_t)j.c[s] * in[(size_t)j.src[s] * A.in_stride + i];
-            }
+            for (int s = 0; s < 4; ++s)
+                if (j.c[s]) v += (uint32_t)j.c[s] * in[(size_t)j.src[s] * A.in_stride + i];
             uint32_t state = v;
             if (tot < 32) {
                 state = v >> (32 - tot - 1);
@@ -110,10 +75,58 @@ __global__ void __launch_bounds__(KM_NT, 2) ks_mma_kernel(const KsMmaArgs P) {
                 state += carry;
                 packed |= (uint32_t)(uint8_t)(int8_t)((int32_t)res - (int32_t)(carry << BL)) << (8 * l);
             }
-            *reinterpret_cast<uint32_t*>(As + g * KM_PITCH + lane * 4) = packed;
+            row[i] = packed;
         }
-        asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+}
+
+constexpr int KM_STAGE = (KM_TM + 4 * KM_TN) * KM_PITCH;      // one ring stage: A tile + 4 plane tiles
+
+__global__ void __launch_bounds__(KM_NT, 2) ks_mma2_kernel(const KsMmaArgs P, const uint8_t* dig) {
+    const KsArgs& A = P.a;
+    extern __shared__ __align__(16) unsigned char km_smem[];
+    __shared__ KsJob jobs[KM_TM];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n = A.n, kN = A.kN, K = kN * KM_L;
+    const int job0 = blockIdx.x * KM_TM, col0 = blockIdx.y * KM_TN;
+    const int njob = min(KM_TM, (int)A.n_jobs - job0);
+    if (tid < KM_TM) {
+        KsJob j = {{0, 0, 0, 0}, {0, 0, 0, 0}, 0, 0, 0};
+        if (tid < njob) j = A.jobs[job0 + tid];
+        jobs[tid] = j;
+    }
+    const int wm = warp & 3, wn = warp >> 2;
+    int acc[4][4][4];
+#pragma unroll
+    for (int nb = 0; nb < 4; ++nb)
+#pragma unroll
+        for (int p = 0; p < 4; ++p)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) acc[nb][p][e] = 0;
+    const uint32_t sm_addr = (uint32_t)__cvta_generic_to_shared(km_smem);
+    auto issue = [&](int k0, int stage) {
+        const uint32_t base = sm_addr + (uint32_t)stage * KM_STAGE;
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {                                   // A: 64 rows x 128 bytes
+            const int q = tid + r * KM_NT, row = q >> 3, part = q & 7;
+            cp_async16(base + (uint32_t)(row * KM_PITCH + part * 16), dig + (size_t)(job0 + row) * K + k0 + part * 16);
+        }
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {                                   // B: 4 planes x 64 columns x 128 bytes
+            const int q = tid + r * KM_NT, p = q >> 9, col = (q >> 3) & 63, part = q & 7;
+            cp_async16(base + (uint32_t)((KM_TM + p * KM_TN + col) * KM_PITCH + part * 16),
+                       P.planes + ((size_t)p * P.npad + col0 + col) * K + k0 + part * 16);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    issue(0, 0);
+    const int nchunk = K / KM_KC;
+    for (int ch = 0; ch < nchunk; ++ch) {
+        if (ch + 1 < nchunk) { issue((ch + 1) * KM_KC, (ch + 1) & 1); asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+        else asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncthreads();
+        const unsigned char* As = km_smem + (ch & 1) * KM_STAGE;
+        const unsigned char* Bs = As + KM_TM * KM_PITCH;
 #pragma unroll
         for (int ks = 0; ks < KM_KC / 32; ++ks) {
             uint32_t a[4];
@@ -132,7 +145,7 @@ __global__ void __launch_bounds__(KM_NT, 2) ks_mma_kernel(const KsMmaArgs P) {
         }
         __syncthreads();
     }
-    // out = (0, ..., 0, body) - sum: fragment rows lane/4 and lane/4 + 8, columns 2 (lane%4) and + 1
+    const uint32_t* in = reinterpret_cast<const uint32_t*>(A.in);
     uint32_t* out = reinterpret_cast<uint32_t*>(A.out);
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
