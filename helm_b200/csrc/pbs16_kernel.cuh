@@ -19,6 +19,12 @@
 #pragma once
 #include "pbs_kernel.cuh"
 
+#ifdef HB_PBS16_DIF
+#define HB_DFT16 dft_regs
+#else
+#define HB_DFT16 dft_regs_dit
+#endif
+
 namespace hb {
 
 __device__ __forceinline__ double2 ldg_nc(const double2* p) {
@@ -53,6 +59,15 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, double2 (&w)[4]) {  //
         w[q] = make_double2(__hiloint2double((int)r[4 * q + 1], (int)r[4 * q]), __hiloint2double((int)r[4 * q + 3], (int)r[4 * q + 2]));
 }
 
+// Byte B of a packed digit word (two's-complement digits) as a double: one I2F.F64.S8 with a byte selector (conversion
+// unit, not the FP64 pipe) instead of PRMT + MOV + DADD for the 2^52 magic-number form of DigPack<true>::get.
+template <int B> __device__ __forceinline__ double cvt_s8(uint32_t p) { return (double)(int8_t)(p >> (8 * B)); }
+#ifdef HB_PBS16_MAGIC_CVT
+#define HB_DIG_BIAS 64u
+#else
+#define HB_DIG_BIAS 0u
+#endif
+
 // Signed decomposition of a u32 torus value into L biased bytes (digit + 64), closed form of tfhe-rs
 // SignedDecomposer (App. A.3): with b = bit (BL-1) of the next residue, carry = (res + 2^(BL-1) - 1 + b) >> BL, hence
 // u = state + 2^(BL-1) - 1 + b gives digit = (u mod 2^BL) - (2^(BL-1) - 1) - b and next state = u >> BL.
@@ -66,7 +81,7 @@ template <int BL, int L> __device__ __forceinline__ void digit_bytes_u32(uint32_
     for (int l = L - 1; l >= 0; --l) {
         const uint32_t b = (s >> (2 * BL - 1)) & 1u;
         const uint32_t u = s + HALF1 + b;
-        byte[l] = (u & MASK) + (64u - HALF1) - b;
+        byte[l] = (u & MASK) + (HB_DIG_BIAS - HALF1) - b;   // biased byte, or the signed digit (low byte = two's complement)
         s = u >> BL;
     }
 }
@@ -208,7 +223,11 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
                     }
 #pragma unroll
                     for (int lev = 0; lev < L; ++lev)
+#ifdef HB_PBS16_MAGIC_CVT
                         pk[lev][part] = by[0][lev] + (by[1][lev] << 8) + (by[2][lev] << 16) + (by[3][lev] << 24);
+#else
+                        pk[lev][part] = __byte_perm(__byte_perm(by[0][lev], by[1][lev], 0x0040), __byte_perm(by[2][lev], by[3][lev], 0x0040), 0x5410);
+#endif
                 }
             } else {
 #pragma unroll
@@ -246,10 +265,18 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
 #pragma unroll
                 for (int part = 0; part < R / 2; ++part) {
                     const DigT p = pk[0][part];
-                    x[2 * part] = cmul_tw<1>(make_double2(Dig::template get<0>(p), Dig::template get<1>(p)), (2 * part) * TWA);
-                    x[2 * part + 1] = cmul_tw<1>(make_double2(Dig::template get<2>(p), Dig::template get<3>(p)), (2 * part + 1) * TWA);
+#ifndef HB_PBS16_MAGIC_CVT
+                    if constexpr (EXT) {
+                        x[2 * part] = cmul_tw<1>(make_double2(cvt_s8<0>(p), cvt_s8<1>(p)), (2 * part) * TWA);
+                        x[2 * part + 1] = cmul_tw<1>(make_double2(cvt_s8<2>(p), cvt_s8<3>(p)), (2 * part + 1) * TWA);
+                    } else
+#endif
+                    {
+                        x[2 * part] = cmul_tw<1>(make_double2(Dig::template get<0>(p), Dig::template get<1>(p)), (2 * part) * TWA);
+                        x[2 * part + 1] = cmul_tw<1>(make_double2(Dig::template get<2>(p), Dig::template get<3>(p)), (2 * part + 1) * TWA);
+                    }
                 }
-                dft_regs<R, 1>(x);
+                HB_DFT16<R, 1>(x);
                 double2 y[R];
                 if constexpr (TMEMW) {
 #pragma unroll
@@ -277,7 +304,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
                 double2 x[R];
 #pragma unroll
                 for (int j0 = 0; j0 < R; ++j0) x[j0] = xc[j0];
-                dft_regs<R, 1>(x);
+                HB_DFT16<R, 1>(x);
 #pragma unroll
                 for (int k1 = 0; k1 < R; ++k1) xc[k1] = x[brev<R>(k1)];
             }
@@ -362,7 +389,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
             double2 x[R];
 #pragma unroll
             for (int k1 = 0; k1 < R; ++k1) x[k1] = xc[k1];
-            dft_regs<R, -1>(x);
+            HB_DFT16<R, -1>(x);
             if constexpr (TMEMW) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
@@ -383,7 +410,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
             double2 x[R];
 #pragma unroll
             for (int k0 = 0; k0 < R; ++k0) x[k0] = xr[k0 * (R + 1) + idx];
-            dft_regs<R, -1>(x);
+            HB_DFT16<R, -1>(x);
 #pragma unroll
             for (int j1 = 0; j1 < R; ++j1) {
                 const double2 z = cmul_tw<-1>(x[brev<R>(j1)], j1 * TWA);

@@ -18,6 +18,14 @@
 #include <stdint.h>
 #include "fft_regs.cuh"
 
+// PBS transforms: the FMA-form decimation-in-time butterflies (fft_regs.cuh) unless -DHB_PBS_DIF; the one-off key
+// transform (bsk_fft_kernel) keeps dft_regs.
+#ifdef HB_PBS_DIF
+#define HB_DFT dft_regs
+#else
+#define HB_DFT dft_regs_dit
+#endif
+
 namespace hb {
 
 struct PbsJob {            // one bootstrap: in = c0*src0 + c1*src1 + (cst on the body)
@@ -345,7 +353,7 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
                 x[2 * part + 1] = cmul_tw<1>(make_double2(Dig::template get<2>(pk), Dig::template get<3>(pk)), (2 * part + 1) * C::TWA);
             }
             HB_PC_MARK(8);
-            dft_regs<RA, 1>(x);
+            HB_DFT<RA, 1>(x);
             HB_PC_MARK(9);
             double2* xr = X + (size_t)grow * XROW;
             // twiddle loads are batched ahead of the stores: X and WA share the dynamic shared array, so the compiler must
@@ -374,7 +382,7 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
             double2 x[RB];
 #pragma unroll
             for (int j0 = 0; j0 < RB; ++j0) x[j0] = xc[j0];
-            dft_regs<RB, 1>(x);
+            HB_DFT<RB, 1>(x);
 #pragma unroll
             for (int k1 = 0; k1 < RB; ++k1) xc[k1] = x[brev<RB>(k1)];
         }
@@ -439,7 +447,7 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
 #pragma unroll
             for (int k1 = 0; k1 < RB; ++k1) x[k1] = xc[k1];
             HB_PC_MARK(11);
-            dft_regs<RB, -1>(x);
+            HB_DFT<RB, -1>(x);
             HB_PC_MARK(12);
 #pragma unroll
             for (int c0 = 0; c0 < RB; c0 += TWCH) {              // as in P1b: loads batched ahead of the stores
@@ -464,7 +472,7 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
 #pragma unroll
             for (int k0 = 0; k0 < RA; ++k0) x[k0] = xr[k0 * (RB + 1) + j0];
             HB_PC_MARK(14);
-            dft_regs<RA, -1>(x);
+            HB_DFT<RA, -1>(x);
             HB_PC_MARK(15);
             if (SPLIT5) {                                  // the tail runs on every thread below: leave z in place
 #pragma unroll

@@ -9,7 +9,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libhelm_b200.so")
+# HB_LIB: a build variant of the same library (kernel A/B measurements, scripts/ab_variants.sh); never a fallback
+LIB_PATH = os.environ.get("HB_LIB") or os.path.join(_HERE, "libhelm_b200.so")
 
 HB_OK = 0
 AND, NAND, OR, NOR, XOR, XNOR, MUX, NOT, COPY, LUT = range(10)
