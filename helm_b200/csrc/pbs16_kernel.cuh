@@ -18,6 +18,7 @@
 // tfhe-rs carry rule with compile-time base_log (profiles/r01_v3_*: the integer ALU pipe bounded that phase).
 #pragma once
 #include "pbs_kernel.cuh"
+#include "digits_u32.cuh"
 
 #ifdef HB_PBS16_DIF
 #define HB_DFT16 dft_regs
@@ -61,31 +62,13 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, double2 (&w)[4]) {  //
 
 // Byte B of a packed digit word (two's-complement digits) as a double: one I2F.F64.S8 with a byte selector (conversion
 // unit, not the FP64 pipe) instead of PRMT + MOV + DADD for the 2^52 magic-number form of DigPack<true>::get.
-template <int B> __device__ __forceinline__ double cvt_s8(uint32_t p) { return (double)(int8_t)(p >> (8 * B)); }
-#ifdef HB_PBS16_MAGIC_CVT
-#define HB_DIG_BIAS 64u
-#else
-#define HB_DIG_BIAS 0u
-#endif
-
-// Signed decomposition of a u32 torus value into L biased bytes (digit + 64), closed form of tfhe-rs
-// SignedDecomposer (App. A.3): with b = bit (BL-1) of the next residue, carry = (res + 2^(BL-1) - 1 + b) >> BL, hence
-// u = state + 2^(BL-1) - 1 + b gives digit = (u mod 2^BL) - (2^(BL-1) - 1) - b and next state = u >> BL.
-// xr = value + 2^(31 - BL*L) (the closest-representable rounding add; the caller folds it into the rotate-subtract).
-// Checked exhaustively against digits_all (tests/test_oracle_kat.py restates it on the CPU side).
-template <int BL, int L> __device__ __forceinline__ void digit_bytes_u32(uint32_t xr, uint32_t (&byte)[L]) {
-    static_assert(BL * L < 32 && BL <= 7, "byte-staged digits");
-    constexpr uint32_t HALF1 = (1u << (BL - 1)) - 1, MASK = (1u << BL) - 1;
-    uint32_t s = xr >> (32 - BL * L);
-#pragma unroll
-    for (int l = L - 1; l >= 0; --l) {
-        const uint32_t b = (s >> (2 * BL - 1)) & 1u;
-        const uint32_t u = s + HALF1 + b;
-        byte[l] = (u & MASK) + (HB_DIG_BIAS - HALF1) - b;   // biased byte, or the signed digit (low byte = two's complement)
-        s = u >> BL;
-    }
+template <int B> __device__ __forceinline__ double cvt_s8(uint32_t p) {
+    if constexpr (B == 0) {      // the cast form compiles byte 0 to two PRMTs + I2F.F64.S16
+        double d;
+        asm("cvt.rn.f64.s8 %0, %1;" : "=d"(d) : "r"(p));
+        return d;
+    } else return (double)(int8_t)(p >> (8 * B));
 }
-
 template <class T, int K, int L, int G, bool TMEMW>
 struct Pbs16Cfg {
     static constexpr int N = 512, M = 256, R = 16;
@@ -214,6 +197,18 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
                 constexpr uint32_t RND = 1u << (31 - BL * L);
 #pragma unroll
                 for (int part = 0; part < R / 2; ++part) {
+#if !defined(HB_PBS16_MAGIC_CVT) && !defined(HB_PBS16_SCALAR_DIGITS)
+                    uint32_t xv[4], pl[L];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int m = 2 * part + (u >> 1) + 16 * (u & 1);        // u: (c), (c+M), (c+16), (c+16+M)
+                        const uint32_t rot = *reinterpret_cast<const uint32_t*>(eb + ((b4 + 64u * m) & (8u * N - 1)));
+                        xv[u] = rot - (uint32_t)ap[idx + R * m] + RND;
+                    }
+                    digit_lanes_u32<BL, L>(xv, pl);
+#pragma unroll
+                    for (int lev = 0; lev < L; ++lev) pk[lev][part] = pl[lev];
+#else
                     uint32_t by[4][L];
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
@@ -227,6 +222,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
                         pk[lev][part] = by[0][lev] + (by[1][lev] << 8) + (by[2][lev] << 16) + (by[3][lev] << 24);
 #else
                         pk[lev][part] = __byte_perm(__byte_perm(by[0][lev], by[1][lev], 0x0040), __byte_perm(by[2][lev], by[3][lev], 0x0040), 0x5410);
+#endif
 #endif
                 }
             } else {
@@ -267,8 +263,13 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
                     const DigT p = pk[0][part];
 #ifndef HB_PBS16_MAGIC_CVT
                     if constexpr (EXT) {
+#if !defined(HB_PBS16_SEPARATE_TWIST) && !defined(HB_PBS16_DIF)
+                        x[2 * part] = make_double2(cvt_s8<0>(p), cvt_s8<1>(p));          // twisted inside the DFT's first stage
+                        x[2 * part + 1] = make_double2(cvt_s8<2>(p), cvt_s8<3>(p));
+#else
                         x[2 * part] = cmul_tw<1>(make_double2(cvt_s8<0>(p), cvt_s8<1>(p)), (2 * part) * TWA);
                         x[2 * part + 1] = cmul_tw<1>(make_double2(cvt_s8<2>(p), cvt_s8<3>(p)), (2 * part + 1) * TWA);
+#endif
                     } else
 #endif
                     {
@@ -276,6 +277,10 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
                         x[2 * part + 1] = cmul_tw<1>(make_double2(Dig::template get<2>(p), Dig::template get<3>(p)), (2 * part + 1) * TWA);
                     }
                 }
+#if !defined(HB_PBS16_SEPARATE_TWIST) && !defined(HB_PBS16_MAGIC_CVT) && !defined(HB_PBS16_DIF)
+                if constexpr (EXT) dft_regs_dit_twisted<R, 1, TWA>(x);
+                else
+#endif
                 HB_DFT16<R, 1>(x);
                 double2 y[R];
                 if constexpr (TMEMW) {

@@ -54,8 +54,12 @@ struct PbsArgs {
 template <class T> struct TorusOps;
 template <> struct TorusOps<uint32_t> {
     static constexpr int BITS = 32;
-    __device__ static __forceinline__ uint32_t round_add(double z) {   // z in LSB units
-        return (uint32_t)__double2loint(z + 6755399441055744.0);
+    __device__ static __forceinline__ uint32_t round_add(double z) {   // z in LSB units, |z| < 2^51
+#ifdef HB_ROUND_MAGIC
+        return (uint32_t)__double2loint(z + 6755399441055744.0);       // DADD on the FP64 pipe
+#else
+        return (uint32_t)__double2ll_rn(z);                            // F2I.S64.F64 (conversion unit), same nearest-even rounding
+#endif
     }
 };
 template <> struct TorusOps<uint64_t> {
