@@ -55,10 +55,10 @@ template <class T> struct TorusOps;
 template <> struct TorusOps<uint32_t> {
     static constexpr int BITS = 32;
     __device__ static __forceinline__ uint32_t round_add(double z) {   // z in LSB units, |z| < 2^51
-#ifdef HB_ROUND_MAGIC
+#ifndef HB_ROUND_F2I
         return (uint32_t)__double2loint(z + 6755399441055744.0);       // DADD on the FP64 pipe
 #else
-        return (uint32_t)__double2ll_rn(z);                            // F2I.S64.F64 (conversion unit), same nearest-even rounding
+        return (uint32_t)__double2ll_rn(z);      // F2I.S64.F64: measured slower (519.4 vs 515.2 ms per 64k-gate level)
 #endif
     }
 };
@@ -353,11 +353,20 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
 #pragma unroll
             for (int part = 0; part < PARTS; ++part) {
                 const DigT pk = dp[part * RB];
+#ifndef HB_PBS_DIF
+                x[2 * part] = make_double2(Dig::template get<0>(pk), Dig::template get<1>(pk));      // twisted in the DFT's first stage
+                x[2 * part + 1] = make_double2(Dig::template get<2>(pk), Dig::template get<3>(pk));
+#else
                 x[2 * part] = cmul_tw<1>(make_double2(Dig::template get<0>(pk), Dig::template get<1>(pk)), (2 * part) * C::TWA);
                 x[2 * part + 1] = cmul_tw<1>(make_double2(Dig::template get<2>(pk), Dig::template get<3>(pk)), (2 * part + 1) * C::TWA);
+#endif
             }
             HB_PC_MARK(8);
+#ifndef HB_PBS_DIF
+            dft_regs_dit_twisted<RA, 1, C::TWA>(x);
+#else
             HB_DFT<RA, 1>(x);
+#endif
             HB_PC_MARK(9);
             double2* xr = X + (size_t)grow * XROW;
             // twiddle loads are batched ahead of the stores: X and WA share the dynamic shared array, so the compiler must
