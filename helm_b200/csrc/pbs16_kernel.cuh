@@ -253,7 +253,11 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
                 for (int j = 0; j <= K; ++j) o1[q][g][j] = make_double2(0.0, 0.0);
         }
 
+#ifdef HB_PBS16_UNROLL_LEV
+#pragma unroll
+#else
 #pragma unroll 1
+#endif
         for (int lev = 0; lev < L; ++lev) {
             // B: twist, radix-16 DFT over j1, inter-stage twiddle (all in registers) ...
             {
