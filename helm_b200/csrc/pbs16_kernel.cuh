@@ -293,7 +293,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
                         double2 w4[4];
                         tmem_ld16(tw_b + 16 * q, w4);
 #pragma unroll
-                        for (int u = 0; u < 4; ++u) y[4 * q + u] = cmul(x[brev<R>(4 * q + u)], w4[u]);
+                        for (int u = 0; u < 4; ++u) y[4 * q + u] = (4 * q + u == 0) ? x[0] : cmul(x[brev<R>(4 * q + u)], w4[u]);   // W(j0, 0) = 1
                     }
                 } else {
 #pragma unroll
@@ -405,7 +405,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
                     double2 w4[4];
                     tmem_ld16(tw_e + 16 * q, w4);
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) xc[4 * q + u] = cmul_conj(x[brev<R>(4 * q + u)], w4[u]);
+                    for (int u = 0; u < 4; ++u) xc[4 * q + u] = (4 * q + u == 0) ? x[0] : cmul_conj(x[brev<R>(4 * q + u)], w4[u]);   // W(0, k0) = 1
                 }
             } else {
 #pragma unroll
