@@ -20,6 +20,16 @@
 #include "pbs_kernel.cuh"
 #include "digits_u32.cuh"
 
+// Left-over MAC items (position, output polynomial): consecutive threads take the K+1 outputs of one position, so a warp's
+// spectrum load covers a third as many distinct addresses (shared-memory broadcast) -- -DHB_PBS16_ITEM_BY_OUTPUT restores
+// the position-minor order.
+#ifdef HB_PBS16_ITEM_BY_OUTPUT
+#define HB_ITEM_POS(item) ((item) % (REM > 0 ? REM : 1))
+#define HB_ITEM_OUT(item) ((item) / (REM > 0 ? REM : 1))
+#else
+#define HB_ITEM_POS(item) ((item) / (K + 1))
+#define HB_ITEM_OUT(item) ((item) % (K + 1))
+#endif
 #ifdef HB_PBS16_DIF
 #define HB_DFT16 dft_regs
 #else
@@ -96,7 +106,8 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
     constexpr int N = C::N, M = C::M, R = 16, NT = C::NT, XROW = C::XROW, AS = C::ASTRIDE, ROWS = (K + 1) * L;
     constexpr int TWA = HB_TW_DEN / (4 * R);
     constexpr bool EXT = C::EXT;
-    constexpr int PP = C::PP, REM = C::REM, I2 = C::I2, NGRP = C::NGRP;
+    constexpr int PP = C::PP, I2 = C::I2, NGRP = C::NGRP;
+    [[maybe_unused]] constexpr int REM = C::REM;
     using Dig = DigPack<sizeof(T) == 4>;
     using DigT = typename Dig::type;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -293,7 +304,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
                         double2 w4[4];
                         tmem_ld16(tw_b + 16 * q, w4);
 #pragma unroll
-                        for (int u = 0; u < 4; ++u) y[4 * q + u] = (4 * q + u == 0) ? x[0] : cmul(x[brev<R>(4 * q + u)], w4[u]);   // W(j0, 0) = 1
+                        for (int u = 0; u < 4; ++u) y[4 * q + u] = cmul(x[brev<R>(4 * q + u)], w4[u]);
                     }
                 } else {
 #pragma unroll
@@ -333,7 +344,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
                         for (int j = 0; j <= K; ++j) b1[r][j] = ldg_nc(bp + (size_t)(r * (K + 1) + j) * M + pos);
                 }
                 if (q < I2) {
-                    const int item = tid + q * NT, pos = PP * NT + item % (REM > 0 ? REM : 1), j2 = item / (REM > 0 ? REM : 1);
+                    const int item = tid + q * NT, pos = PP * NT + HB_ITEM_POS(item), j2 = HB_ITEM_OUT(item);
 #pragma unroll
                     for (int r = 0; r <= K; ++r) b2[r] = ldg_nc(bp + (size_t)(r * (K + 1) + j2) * M + pos);
                 }
@@ -357,7 +368,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
                     }
                 }
                 if (q < I2) {
-                    const int item = tid + q * NT, s2 = spos(PP * NT + item % (REM > 0 ? REM : 1));
+                    const int item = tid + q * NT, s2 = spos(PP * NT + HB_ITEM_POS(item));
 #pragma unroll
                     for (int r = 0; r <= K; ++r) {
 #pragma unroll
@@ -386,7 +397,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
         }
 #pragma unroll
         for (int q = 0; q < I2; ++q) {
-            const int item = tid + q * NT, s2 = spos(PP * NT + item % (REM > 0 ? REM : 1)), j2 = item / (REM > 0 ? REM : 1);
+            const int item = tid + q * NT, s2 = spos(PP * NT + HB_ITEM_POS(item)), j2 = HB_ITEM_OUT(item);
 #pragma unroll
             for (int g = 0; g < G; ++g) X[((size_t)g * (K + 1) + j2) * XROW + s2] = o2[q][g];
         }
@@ -405,7 +416,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
                     double2 w4[4];
                     tmem_ld16(tw_e + 16 * q, w4);
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) xc[4 * q + u] = (4 * q + u == 0) ? x[0] : cmul_conj(x[brev<R>(4 * q + u)], w4[u]);   // W(0, k0) = 1
+                    for (int u = 0; u < 4; ++u) xc[4 * q + u] = cmul_conj(x[brev<R>(4 * q + u)], w4[u]);
                 }
             } else {
 #pragma unroll
