@@ -70,6 +70,23 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, double2 (&w)[4]) {  //
         w[q] = make_double2(__hiloint2double((int)r[4 * q + 1], (int)r[4 * q]), __hiloint2double((int)r[4 * q + 3], (int)r[4 * q + 2]));
 }
 
+// The same load split into issue and wait, so the next 16 columns are in flight while the current ones are used
+// (-DHB_PBS16_TMEM_PIPE).  The wait names the registers as in/out operands: nothing may read them before it.
+__device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                 : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16_wait(uint32_t (&r)[16]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                   "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
+                 :: "memory");
+}
+__device__ __forceinline__ double2 tmem_pair(const uint32_t (&r)[16], int u) {
+    return make_double2(__hiloint2double((int)r[4 * u + 1], (int)r[4 * u]), __hiloint2double((int)r[4 * u + 3], (int)r[4 * u + 2]));
+}
 // Byte B of a packed digit word (two's-complement digits) as a double: one I2F.F64.S8 with a byte selector (conversion
 // unit, not the FP64 pipe) instead of PRMT + MOV + DADD for the 2^52 magic-number form of DigPack<true>::get.
 template <int B> __device__ __forceinline__ double cvt_s8(uint32_t p) {
@@ -299,6 +316,17 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
                 HB_DFT16<R, 1>(x);
                 double2 y[R];
                 if constexpr (TMEMW) {
+#ifdef HB_PBS16_TMEM_PIPE
+                    uint32_t rw[2][16];
+                    tmem_ld16_issue(tw_b, rw[0]);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        tmem_ld16_wait(rw[q & 1]);
+                        if (q < 3) tmem_ld16_issue(tw_b + 16 * (q + 1), rw[(q + 1) & 1]);
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) y[4 * q + u] = cmul(x[brev<R>(4 * q + u)], tmem_pair(rw[q & 1], u));
+                    }
+#else
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         double2 w4[4];
@@ -306,6 +334,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
 #pragma unroll
                         for (int u = 0; u < 4; ++u) y[4 * q + u] = cmul(x[brev<R>(4 * q + u)], w4[u]);
                     }
+#endif
                 } else {
 #pragma unroll
                     for (int k0 = 0; k0 < R; ++k0) y[k0] = cmul(x[brev<R>(k0)], W[k0 * (R + 1) + idx]);
@@ -411,6 +440,17 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
             for (int k1 = 0; k1 < R; ++k1) x[k1] = xc[k1];
             HB_DFT16<R, -1>(x);
             if constexpr (TMEMW) {
+#ifdef HB_PBS16_TMEM_PIPE
+                uint32_t rw[2][16];
+                tmem_ld16_issue(tw_e, rw[0]);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    tmem_ld16_wait(rw[q & 1]);
+                    if (q < 3) tmem_ld16_issue(tw_e + 16 * (q + 1), rw[(q + 1) & 1]);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) xc[4 * q + u] = cmul_conj(x[brev<R>(4 * q + u)], tmem_pair(rw[q & 1], u));
+                }
+#else
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     double2 w4[4];
@@ -418,6 +458,7 @@ __global__ void __launch_bounds__(G * (K + 1) * 16, MINB) pbs16_kernel(const Pbs
 #pragma unroll
                     for (int u = 0; u < 4; ++u) xc[4 * q + u] = cmul_conj(x[brev<R>(4 * q + u)], w4[u]);
                 }
+#endif
             } else {
 #pragma unroll
                 for (int j0 = 0; j0 < R; ++j0) xc[j0] = cmul_conj(x[brev<R>(j0)], W[idx * (R + 1) + j0]);
