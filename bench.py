@@ -201,7 +201,7 @@ def iscas_latency(name, device, params=PARAM_SET):
     sess = H.Session(params, device=device, seed=5)
     want = circ.evaluate()
     best = None
-    for rep in range(8):      # best of 8: the first runs after the host-only CPU leg see the GPU clocks ramping up
+    for rep in range(8):
         got, secs = sess.run(circ)
         assert all(bool(got[k]) == bool(want[k]) for k in got), "c7552: decrypted outputs differ from the plaintext netlist"
         best = secs if best is None or secs[1] < best[1] else best
