@@ -35,7 +35,8 @@ template <int BL, int L> __device__ __forceinline__ void digit_bytes_u32(uint32_
 // plain 32-bit adds -- every lane value stays below 2^7, so nothing crosses a lane.  pk[lev] receives the level-lev digits
 // of x[0..3] as two's-complement bytes (the operand format of I2F.F64.S8).  About 42 ALU instructions per four values
 // against 85 for four scalar chains + packing; tests/test_digit_lanes_cpu.py checks both against the recurrence exhaustively.
-template <int BL, int L> __device__ __forceinline__ void digit_lanes_u32(const uint32_t (&x)[4], uint32_t (&pk)[L]) {
+// SIGNED = false: bytes biased by 64 instead (the DigPack<true> staging format of pbs_kernel), which also drops the final XOR.
+template <int BL, int L, bool SIGNED = true> __device__ __forceinline__ void digit_lanes_u32(const uint32_t (&x)[4], uint32_t (&pk)[L]) {
     static_assert(BL * L <= 24 && BL >= 2 && BL <= 7 && L >= 2, "fields must lie in bytes 1..3; lane sums must stay below 2^8");
     constexpr uint32_t M1 = 0x01010101u, MASK = ((1u << BL) - 1) * M1, HALF1 = ((1u << (BL - 1)) - 1) * M1;
     const uint32_t p01 = __byte_perm(x[0], x[1], 0x7632), p23 = __byte_perm(x[2], x[3], 0x7632);
@@ -63,7 +64,8 @@ template <int BL, int L> __device__ __forceinline__ void digit_lanes_u32(const u
             B = (Nx >> (BL - 1)) & M1;
         }
         const uint32_t U = (E & MASK) + HALF1 + B;
-        pk[lev] = ((U & MASK) + (0x80u * M1 - HALF1) - B) ^ 0x80808080u;
+        if (SIGNED) pk[lev] = ((U & MASK) + (0x80u * M1 - HALF1) - B) ^ 0x80808080u;
+        else pk[lev] = (U & MASK) + (0x40u * M1 - HALF1) - B;
         if (lev > 0) E = Nx + ((U >> BL) & M1);
     }
 }

@@ -47,7 +47,9 @@ template <int BL, int L> static long check() {
             x[u] = (other << (32 - BL * L)) | ((lcg >> 3) & ((1u << (32 - BL * L)) - 1));
             xr[u] = x[u] + RND;
         }
+        uint32_t pb[L];
         hb::digit_lanes_u32<BL, L>(xr, pk);
+        hb::digit_lanes_u32<BL, L, false>(xr, pb);      // bytes biased by 64 (pbs_kernel's staging format)
         for (int u = 0; u < 4; ++u) {
             int32_t want[L];
             uint32_t by[L];
@@ -56,7 +58,8 @@ template <int BL, int L> static long check() {
             for (int lev = 0; lev < L; ++lev) {
                 const int32_t lane = (int8_t)(pk[lev] >> (8 * u));
                 const int32_t scal = (int8_t)(by[lev] & 0xff);
-                if (lane != want[lev] || scal != want[lev]) {
+                const int32_t biased = (int32_t)((pb[lev] >> (8 * u)) & 0xff) - 64;
+                if (lane != want[lev] || scal != want[lev] || biased != want[lev]) {
                     printf("mismatch BL=%d L=%d x=%08x lane %d lev %d: lanes %d scalar %d reference %d\n", BL, L, x[u], u, lev, lane, scal, want[lev]);
                     exit(1);
                 }
