@@ -33,7 +33,25 @@ sys.path.insert(0, ROOT)
 W_DEFAULT, DEPTH = 65536, 32
 PARAM_SET = "boolean_default"
 F_CMUX = 196608.0            # flops per CMUX step, boolean default
-NCU_DRAM_BYTES_PER_LAUNCH = 15.144161e9 + 396.515328e6     # profiles/r01_v8_pbs16_kernel_fullwidth_ncu.txt
+
+
+def ncu_traffic(kernel_prefix, width):
+    """roofline.traffic: dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel at this width, from
+    the newest committed record profiles/*_traffic.json (written by scripts/ncu_traffic.py out of an `ncu --set full` capture).
+    None when no record matches the kernel and width that were just measured -- a stale constant is worse than none."""
+    import glob
+    best = None
+    for f in sorted(glob.glob(os.path.join(ROOT, "profiles", "*_traffic.json"))):
+        try:
+            r = json.load(open(f))
+        except Exception:
+            continue
+        if str(r.get("kernel", "")).startswith(kernel_prefix) and int(r.get("gates_per_launch", -1)) == int(width):
+            best = (r, os.path.relpath(f, ROOT))
+    if best is None:
+        return None, None
+    r, f = best
+    return float(r["dram_bytes_read"]) + float(r["dram_bytes_write"]), "%s (%s)" % (f, r.get("source", "ncu --set full"))
 GATE_OPS = 6                 # AND NAND OR NOR XOR XNOR
 
 
@@ -123,27 +141,43 @@ def cpu_level_sample(K, O, wires0, level_gates, count, mode):
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU path (restated; tfhe-rs itself cannot be built here) on the host cores."""
+    """--impl reference: the reference's CPU path (restated; tfhe-rs itself cannot be built here) on the host cores.
+    The loop it stands for is gates.par_iter_mut() over one level, /root/reference/src/circuit.rs:531.
+    Under torch.distributed.run (N > 1) only rank 0 works, with every online core: the launcher exports OMP_NUM_THREADS=1
+    to its workers, so the OpenMP team is set explicitly, and the per-step sample is sized from a calibration step so that
+    the whole arm takes about REF_BUDGET_S seconds whatever the core count."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     from oracle import oracle as O
+    threads = O.set_threads(0)
     K = O.Keys(PARAM_SET, seed=3)
     W = args.width
     bits0 = (splitmix64(2, W) & np.uint64(1)).astype(np.uint8)
-    threads = os.cpu_count() or 1
-    sample = max(threads, min(W, args.cpu_gates if args.cpu_gates else 64 * threads))       # ~2-3 s of host work per step
-    # only the wires the sample reads need to exist: encrypt level 0 lazily
-    times = []
-    for s in range(args.warmup + args.steps):
+
+    def step(s, sample):
         lvl = s % DEPTH + 1
         ops, in0, in1 = synth_level(lvl, W)
-        need = np.unique(np.concatenate([in0[:sample], in1[:sample]]))
+        need = np.unique(np.concatenate([in0[:sample], in1[:sample]]))          # only the wires the sample reads
         remap = np.zeros(W, dtype=np.uint32); remap[need] = np.arange(len(need), dtype=np.uint32)
         w0 = K.enc_bool_batch(bits0[need], 10_000 + 7 * s)
-        dt, threads, out = cpu_level_sample(K, O, w0, (ops, remap[in0], remap[in1]), sample, O.FFT)
+        dt, used, out = cpu_level_sample(K, O, w0, (ops, remap[in0], remap[in1]), sample, O.FFT)
         want = plain_gate(ops[:sample], bits0[in0[:sample]], bits0[in1[:sample]])
         assert np.array_equal(K.dec_bool_batch(out), want), "reference arm: wrong gate outputs"
+        return dt, used
+
+    REF_BUDGET_S = 45.0
+    dt, used = step(0, 2 * threads)                       # calibration (also builds the Fourier key): untimed
+    dt, used = step(0, 4 * threads)
+    rate = 4 * threads / dt
+    if args.cpu_gates:
+        sample = min(W, args.cpu_gates)
+    else:
+        sample = int(rate * REF_BUDGET_S / max(1, args.warmup + args.steps))
+        sample = max(threads, min(W, (sample // threads) * threads))
+    times = []
+    for s in range(args.warmup + args.steps):
+        dt, used = step(s, sample)
         if s >= args.warmup:
             times.append(dt)
     tot = float(sum(times))
@@ -152,9 +186,11 @@ def run_reference(args):
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / len(times),
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": workload_config(args, 1),
-            "cpu_baseline": {"value": v, "unit": "PBS/s", "cores": threads, "kind": "port",
-                             "sample": "%d gates of the level per step (of %d), oracle f64-FFT, OpenMP one gate per thread"
-                                       % (sample, W)},
+            "cpu_baseline": {"value": v, "unit": "PBS/s", "cores": int(used), "kind": "port",
+                             "sample": "%d gates of the level per step (of %d), oracle f64-FFT, OpenMP one gate per thread "
+                                       "(team of %d set explicitly; host has %d cores); tfhe-rs itself is unavailable on this box -- "
+                                       "its hand-vectorised FFT is typically 2-3x faster per core than this port"
+                                       % (sample, W, used, os.cpu_count() or 1)},
             "e2e": {"value": v, "unit": "PBS/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     emit_line(line)
@@ -382,15 +418,21 @@ def main():
     # ---- end to end through the C ABI with host buffers (pinned), copies inside the timed region
     e2e = None
     if not args.no_e2e:
-        hin = torch.empty((W, words), dtype=torch.int32).pin_memory()
+        # every rank holds 1/N of the level's input ciphertexts in pinned host memory (the rows of its own gate slice of the
+        # previous level) and wants its own slice of the outputs back: H2D of W/N rows, all-gather of the inputs over NVLink
+        # (each gate reads any wire of the previous level), evaluation, all-gather of the outputs (what the next level needs
+        # on every rank), D2H of W/N rows
+        hin = torch.empty((Wr, words), dtype=torch.int32).pin_memory()
         hout = torch.empty((Wr, words), dtype=torch.int32).pin_memory()
         hin_np = hin.numpy().view(eng.dtype); hout_np = hout.numpy().view(eng.dtype)
-        hin_np[:] = ct0
+        hin_np[:] = ct0[g0:g0 + Wr]
 
         def step_e2e(s):
             lvl = s % DEPTH + 1
-            wires.write_rows((lvl - 1) * W, hin_np)            # H2D: the level's input wires (host -> HBM)
+            wires.write_rows((lvl - 1) * W + g0, hin_np)       # H2D: this rank's share of the level's input wires
+            exchange(lvl - 1)                                  # inputs visible on every rank
             eng.eval_level(wires, levels[lvl - 1])
+            exchange(lvl)                                      # outputs visible on every rank
             wires.read_rows(lvl * W + g0, hout_np)             # D2H: this rank's output ciphertexts (syncs)
         for s in range(args.warmup):
             step_e2e(0)
@@ -411,7 +453,9 @@ def main():
         if not ok:
             raise SystemExit("bench.py: e2e outputs decrypt wrong")
         e2e = {"value": W * args.steps / (float(t.item()) * 1e-3), "unit": "PBS/s",
-               "h2d_bytes_per_step": int(hin_np.nbytes + levels[0].nbytes), "d2h_bytes_per_step": int(hout_np.nbytes),
+               "h2d_bytes_per_step": int(world * (hin_np.nbytes + levels[0].nbytes)), "d2h_bytes_per_step": int(world * hout_np.nbytes),
+               "per_rank": "each of the %d rank(s) copies 1/%d of the level's inputs up and its own outputs down; byte counts "
+                           "are the whole job's" % (world, world),
                "ms_per_step": float(t.item()) / args.steps}
 
     # ---- CPU baseline (rank 0, N = 1 only): bounded sample of level 1 on the host cores
@@ -447,6 +491,11 @@ def main():
         flops_per_launch = Wr * K.n * F_CMUX
         ach = flops_per_launch / (pbs_ms * 1e-3) / 1e12 if pbs_ms > 0 else None
         bsk_bytes = K.n * 9 * 3 * 256 * 16
+        traffic, traffic_src = ncu_traffic("pbs16_kernel", Wr) if world == 1 else (None, None)
+        # independent anchor for the in-run DFMA measurement: 64 FP64 lanes per SM x 2 flop x the SM clock sampled under load
+        sm_count = torch.cuda.get_device_properties(local).multi_processor_count
+        sm_mhz = (clocks or {}).get("sm_mhz") or 0.0
+        peak_theory = sm_count * 64 * 2 * sm_mhz * 1e6 / 1e12 if sm_mhz else None
         line = {"metric": "PBS/s (batched gate bootstraps)", "value": value, "unit": "PBS/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
@@ -454,12 +503,12 @@ def main():
                 "roofline": {"bound": "fp64", "kernel": "pbs16_kernel<u32,K=2,L=3,BL=6,G=4> (blind rotation + sample extract)",
                              "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s",
                              "frac": (ach / fp64_peak) if ach else None,
-                             "traffic": NCU_DRAM_BYTES_PER_LAUNCH if (world == 1 and W == W_DEFAULT) else None,
-                             "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one full-width launch, "
-                                               "profiles/r01_v8_pbs16_kernel_fullwidth_ncu.txt (the kernel is FP64-bound: the "
-                                               "Fourier key stays in L2 at a 98.3 % hit rate, its misses make DRAM traffic ~30 GB/s)",
+                             "peak_theoretical": peak_theory,
+                             "frac_theoretical": (ach / peak_theory) if (ach and peak_theory) else None,
+                             "traffic": traffic, "traffic_source": traffic_src,
                              "peak_source": "measured in this run: register-resident DFMA loop (hb_measure_fp64_peak); "
-                                            "MEASURED_PEAKS.json has no FP64 entry",
+                                            "MEASURED_PEAKS.json has no FP64 entry.  peak_theoretical = SMs x 64 FP64 lanes x 2 "
+                                            "flop x the median SM clock nvidia-smi sampled during the timed region",
                              "flops_per_launch": flops_per_launch, "kernel_ms": pbs_ms, "ks_kernel_ms": ks_ms, "gap_ms": gap_ms, "host_enqueue_ms": enqueue_ms,
                              "hbm_floor_ms": 1e3 * (bsk_bytes + 3.0 * Wr * words * 4) / (hbm_peak_gbs() * 1e9)},
                 "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,

@@ -4,6 +4,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
+#include <atomic>
 #include <string>
 #include <type_traits>
 #include <vector>
@@ -23,6 +25,21 @@ using namespace hb;
 
 namespace {
 thread_local std::string g_create_error;
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a per-DEVICE property of a kernel: one flag per (kernel, device), so a
+// second context on another GPU of the same process opts in too (the current device is the launching context's).
+struct SmemOptIn {
+    std::atomic<uint64_t> done{0};
+    template <class K> cudaError_t ensure(K kern, size_t bytes) {
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return e;
+        if ((done.load(std::memory_order_acquire) >> dev) & 1ull) return cudaSuccess;
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+        if (e == cudaSuccess) done.fetch_or(1ull << dev, std::memory_order_release);
+        return e;
+    }
+};
 
 struct DevBuf {
     void* p = nullptr; size_t cap = 0;
@@ -52,8 +69,17 @@ struct PinBuf {
 };
 }  // namespace
 
+constexpr int NSLOT = 4;
+struct JobSlot {
+    PinBuf pin; DevBuf dev; cudaEvent_t done = nullptr;
+    cudaEvent_t t[3] = {nullptr, nullptr, nullptr};   // brackets of the two phases of one level
+    bool pending = false; int first_is_pbs = 1;
+};
+struct CtxExtra { JobSlot slots[NSLOT]; uint64_t next = 0; };
+
 struct hb_ctx {
     int device = 0;
+    CtxExtra extra;                        // job-descriptor ring (owned by the context: contexts share no mutable state)
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     hb_params p{};
@@ -63,6 +89,7 @@ struct hb_ctx {
     DevBuf ksk_planes, ks_dig; int ksk_npad = 0;   // byte planes of the KSK for the tensor-core keyswitch (u32, ks_level 4)
     DevBuf scratch_a, scratch_b;           // PBS->KS (order 0) or KS->PBS (order 1) intermediates
     DevBuf atil;                           // switched masks of the running PBS batch (pbs16_kernel)
+    DevBuf lin_stage;                      // staging rows of a linear batch with read-after-write between its jobs
     DevBuf jobs_dev, stage_dev, idx_dev;
     PinBuf jobs_pin, stage_pin;
     hb_stats_t stats{};
@@ -110,11 +137,16 @@ template <class T> __global__ void repack_rows(T* dst, uint32_t dstride, const T
     }
 }
 struct LinJob { uint32_t src, dst; int32_t c; uint32_t pad; uint64_t cst; };   // dst = c*src + cst(body); c==0: trivial
-template <class T> __global__ void linear_rows(T* w, uint32_t stride, const LinJob* jobs, uint32_t cnt, uint32_t words) {
+// MODE 0: in place on the wire array.  MODE 1 / 2: the two halves of a staged batch (results to scratch row r, then scratch row r
+// to its wire) -- used when a job reads a row another job of the batch writes (chained DFFs q2 <= q1 <= d in the DFF level), so that
+// every job sees the pre-batch values like the reference's clone-then-write loop (src/circuit.rs:532-540).
+template <class T, int MODE> __global__ void linear_rows(T* w, uint32_t stride, T* scratch, const LinJob* jobs, uint32_t cnt, uint32_t words) {
     for (uint32_t r = blockIdx.y; r < cnt; r += gridDim.y) {
         const LinJob j = jobs[r];
-        const T* s = w + (size_t)j.src * stride; T* d = w + (size_t)j.dst * stride;
+        const T* s = MODE == 2 ? scratch + (size_t)r * stride : w + (size_t)j.src * stride;
+        T* d = MODE == 1 ? scratch + (size_t)r * stride : w + (size_t)j.dst * stride;
         for (uint32_t x = blockIdx.x * blockDim.x + threadIdx.x; x < words; x += gridDim.x * blockDim.x) {
+            if (MODE == 2) { d[x] = s[x]; continue; }
             T v = j.c ? (T)(int64_t)j.c * s[x] : (T)0;
             if (x == words - 1) v += (T)j.cst;
             d[x] = v;
@@ -123,11 +155,13 @@ template <class T> __global__ void linear_rows(T* w, uint32_t stride, const LinJ
 }
 
 // dst = sum_s c[s]*src[s] + cst(body), up to 4 sources (job layout shared with the keyswitch prologue)
-template <class T> __global__ void lincomb_rows(T* w, uint32_t stride, const KsJob* jobs, uint32_t cnt, uint32_t words) {
+// MODE as in linear_rows (0 in place, 1 results to scratch row r, 2 scratch row r to its wire)
+template <class T, int MODE> __global__ void lincomb_rows(T* w, uint32_t stride, T* scratch, const KsJob* jobs, uint32_t cnt, uint32_t words) {
     for (uint32_t r = blockIdx.y; r < cnt; r += gridDim.y) {
         const KsJob j = jobs[r];
-        T* d = w + (size_t)j.dst * stride;
+        T* d = MODE == 1 ? scratch + (size_t)r * stride : w + (size_t)j.dst * stride;
         for (uint32_t x = blockIdx.x * blockDim.x + threadIdx.x; x < words; x += gridDim.x * blockDim.x) {
+            if (MODE == 2) { d[x] = scratch[(size_t)r * stride + x]; continue; }
             T v = 0;
 #pragma unroll
             for (int s = 0; s < 4; ++s) if (j.c[s]) v += (T)(int64_t)j.c[s] * w[(size_t)j.src[s] * stride + x];
@@ -178,12 +212,8 @@ struct Inst {
     static size_t smem(int n) { return STAGE ? C::smem_bytes_staged(n) : C::smem_bytes(n); }
     static cudaError_t launch(const PbsArgs& a, cudaStream_t s, size_t smem) {
         auto kern = pbs_kernel<T, N, K, L, RA, RB, G, NT, MINB, STAGE>;
-        static bool attr_done = false;
-        if (!attr_done) {
-            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PBS_DYN_SMEM_MAX);
-            if (e != cudaSuccess) return e;
-            attr_done = true;
-        }
+        static SmemOptIn opt;
+        if (cudaError_t e = opt.ensure(kern, PBS_DYN_SMEM_MAX)) return e;
         const unsigned grid = (a.n_jobs + G - 1) / G;
         kern<<<grid, NT, smem, s>>>(a);
         return cudaGetLastError();
@@ -203,12 +233,8 @@ struct Inst16 {
     static size_t smem(int n) { return C::smem_bytes(n); }
     static cudaError_t launch(const PbsArgs& a, cudaStream_t s, size_t smem) {
         auto kern = pbs16_kernel<T, K, L, BL, G, MINB, TMEMW>;
-        static bool attr_done = false;
-        if (!attr_done) {
-            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-            if (e != cudaSuccess) return e;
-            attr_done = true;
-        }
+        static SmemOptIn opt;
+        if (cudaError_t e = opt.ensure(kern, 227 * 1024)) return e;
         const unsigned grid = (a.n_jobs + G - 1) / G;
         kern<<<grid, C::NT, smem, s>>>(a);
         return cudaGetLastError();
@@ -240,16 +266,7 @@ int find_shape(const hb_params& p) {
 // ================================================================ internal launch helpers
 namespace {
 
-constexpr int NSLOT = 4;
-struct JobSlot {
-    PinBuf pin; DevBuf dev; cudaEvent_t done = nullptr;
-    cudaEvent_t t[3] = {nullptr, nullptr, nullptr};   // brackets of the two phases of one level
-    bool pending = false; int first_is_pbs = 1;
-};
-struct CtxExtra { JobSlot slots[NSLOT]; uint64_t next = 0; };
-// kept outside hb_ctx's public-ish layout; one per context
-std::vector<std::pair<hb_ctx*, CtxExtra*>> g_extra;
-CtxExtra* extra_of(hb_ctx* c) { for (auto& e : g_extra) if (e.first == c) return e.second; return nullptr; }
+CtxExtra* extra_of(hb_ctx* c) { return &c->extra; }
 
 // folds a finished slot's phase timings into the context totals (slot->done must have completed)
 void fold_timing(hb_ctx* c, JobSlot& s, JobSlot* next = nullptr) {
@@ -362,9 +379,9 @@ hb_status launch_ks(hb_ctx* c, const void* in, uint32_t in_stride, void* out, ui
         const uint32_t rows_pad = grid.x * KM_TM;
         CU(c, c->ks_dig.ensure((size_t)rows_pad * a.kN * KM_L));
         ks_digits_kernel<<<rows_pad < 65535u ? rows_pad : 65535u, 256, 0, c->stream>>>(m.a, (uint8_t*)c->ks_dig.p, rows_pad);
-        static bool attr2 = false;
+        static SmemOptIn opt2;
         const size_t smem2 = 2 * (size_t)KM_STAGE;
-        if (!attr2) { CU(c, cudaFuncSetAttribute(ks_mma2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2)); attr2 = true; }
+        CU(c, opt2.ensure(ks_mma2_kernel, smem2));
         ks_mma2_kernel<<<grid, KM_NT, smem2, c->stream>>>(m, (const uint8_t*)c->ks_dig.p);
         CU(c, cudaGetLastError());
         c->stats.kernel_launches++;
@@ -398,24 +415,65 @@ hb_status launch_ks(hb_ctx* c, const void* in, uint32_t in_stride, void* out, ui
     return HB_OK;
 }
 
-hb_status launch_lin(hb_ctx* c, void* w, uint32_t stride, const LinJob* jobs, uint32_t cnt, uint32_t words) {
-    if (!cnt) return HB_OK;
-    dim3 grid((words + 255) / 256, cnt < 32768 ? cnt : 32768);
-    if (c->p.torus_bits == 32) linear_rows<uint32_t><<<grid, 256, 0, c->stream>>>((uint32_t*)w, stride, jobs, cnt, words);
-    else linear_rows<uint64_t><<<grid, 256, 0, c->stream>>>((uint64_t*)w, stride, jobs, cnt, words);
-    CU(c, cudaGetLastError());
-    c->stats.kernel_launches++;
-    return HB_OK;
+// true iff some job of the batch reads a row that another job of the batch writes
+bool lin_hazard(const std::vector<LinJob>& lj) {
+    if (lj.size() < 2) return false;
+    std::vector<uint32_t> dst(lj.size());
+    for (size_t i = 0; i < lj.size(); ++i) dst[i] = lj[i].dst;
+    std::sort(dst.begin(), dst.end());
+    for (const LinJob& j : lj)
+        if (j.c && j.src != j.dst && std::binary_search(dst.begin(), dst.end(), j.src)) return true;
+    return false;
 }
 
-hb_status launch_lincomb(hb_ctx* c, void* w, uint32_t stride, const KsJob* jobs, uint32_t cnt, uint32_t words) {
-    if (!cnt) return HB_OK;
+template <class T> hb_status launch_lin_t(hb_ctx* c, void* w, uint32_t stride, const LinJob* jobs, uint32_t cnt, uint32_t words, bool staged) {
     dim3 grid((words + 255) / 256, cnt < 32768 ? cnt : 32768);
-    if (c->p.torus_bits == 32) lincomb_rows<uint32_t><<<grid, 256, 0, c->stream>>>((uint32_t*)w, stride, jobs, cnt, words);
-    else lincomb_rows<uint64_t><<<grid, 256, 0, c->stream>>>((uint64_t*)w, stride, jobs, cnt, words);
+    if (!staged) {
+        linear_rows<T, 0><<<grid, 256, 0, c->stream>>>((T*)w, stride, nullptr, jobs, cnt, words);
+        c->stats.kernel_launches++;
+    } else {
+        CU(c, c->lin_stage.ensure((size_t)cnt * stride * sizeof(T)));
+        linear_rows<T, 1><<<grid, 256, 0, c->stream>>>((T*)w, stride, (T*)c->lin_stage.p, jobs, cnt, words);
+        linear_rows<T, 2><<<grid, 256, 0, c->stream>>>((T*)w, stride, (T*)c->lin_stage.p, jobs, cnt, words);
+        c->stats.kernel_launches += 2;
+    }
     CU(c, cudaGetLastError());
-    c->stats.kernel_launches++;
     return HB_OK;
+}
+hb_status launch_lin(hb_ctx* c, void* w, uint32_t stride, const LinJob* jobs, uint32_t cnt, uint32_t words, bool staged = false) {
+    if (!cnt) return HB_OK;
+    return c->p.torus_bits == 32 ? launch_lin_t<uint32_t>(c, w, stride, jobs, cnt, words, staged)
+                                 : launch_lin_t<uint64_t>(c, w, stride, jobs, cnt, words, staged);
+}
+
+bool lincomb_hazard(const std::vector<KsJob>& kj) {
+    if (kj.size() < 2) return false;
+    std::vector<uint32_t> dst(kj.size());
+    for (size_t i = 0; i < kj.size(); ++i) dst[i] = kj[i].dst;
+    std::sort(dst.begin(), dst.end());
+    for (const KsJob& j : kj)
+        for (int s = 0; s < 4; ++s)
+            if (j.c[s] && j.src[s] != j.dst && std::binary_search(dst.begin(), dst.end(), j.src[s])) return true;
+    return false;
+}
+template <class T> hb_status launch_lincomb_t(hb_ctx* c, void* w, uint32_t stride, const KsJob* jobs, uint32_t cnt, uint32_t words, bool staged) {
+    dim3 grid((words + 255) / 256, cnt < 32768 ? cnt : 32768);
+    if (!staged) {
+        lincomb_rows<T, 0><<<grid, 256, 0, c->stream>>>((T*)w, stride, nullptr, jobs, cnt, words);
+        c->stats.kernel_launches++;
+    } else {
+        CU(c, c->lin_stage.ensure((size_t)cnt * stride * sizeof(T)));
+        lincomb_rows<T, 1><<<grid, 256, 0, c->stream>>>((T*)w, stride, (T*)c->lin_stage.p, jobs, cnt, words);
+        lincomb_rows<T, 2><<<grid, 256, 0, c->stream>>>((T*)w, stride, (T*)c->lin_stage.p, jobs, cnt, words);
+        c->stats.kernel_launches += 2;
+    }
+    CU(c, cudaGetLastError());
+    return HB_OK;
+}
+hb_status launch_lincomb(hb_ctx* c, void* w, uint32_t stride, const KsJob* jobs, uint32_t cnt, uint32_t words, bool staged = false) {
+    if (!cnt) return HB_OK;
+    return c->p.torus_bits == 32 ? launch_lincomb_t<uint32_t>(c, w, stride, jobs, cnt, words, staged)
+                                 : launch_lincomb_t<uint64_t>(c, w, stride, jobs, cnt, words, staged);
 }
 
 }  // namespace
@@ -439,12 +497,10 @@ hb_status hb_ctx_create(int32_t device, hb_ctx** out) {
     CU(nullptr, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     for (auto& ev : c->ev) CU(nullptr, cudaEventCreate(&ev));
     CU(nullptr, cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
-    CtxExtra* ex = new CtxExtra();
-    for (auto& s : ex->slots) {
+    for (auto& s : c->extra.slots) {
         CU(nullptr, cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
         for (auto& t : s.t) CU(nullptr, cudaEventCreate(&t));
     }
-    g_extra.emplace_back(c, ex);
     *out = c;
     return HB_OK;
 }
@@ -453,16 +509,12 @@ hb_status hb_ctx_destroy(hb_ctx* c) {
     if (!c) return HB_ERR_ARG;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    for (DevBuf* b : {&c->bsk_f, &c->ksk, &c->ksk_planes, &c->ks_dig, &c->wtab, &c->scratch_a, &c->scratch_b, &c->atil, &c->jobs_dev, &c->stage_dev, &c->idx_dev}) b->release();
+    for (DevBuf* b : {&c->bsk_f, &c->ksk, &c->ksk_planes, &c->ks_dig, &c->wtab, &c->scratch_a, &c->scratch_b, &c->atil, &c->lin_stage, &c->jobs_dev, &c->stage_dev, &c->idx_dev}) b->release();
     c->jobs_pin.release(); c->stage_pin.release();
-    for (size_t i = 0; i < g_extra.size(); ++i)
-        if (g_extra[i].first == c) {
-            for (auto& s : g_extra[i].second->slots) {
-                s.pin.release(); s.dev.release(); cudaEventDestroy(s.done);
-                for (auto& t : s.t) cudaEventDestroy(t);
-            }
-            delete g_extra[i].second; g_extra.erase(g_extra.begin() + i); break;
-        }
+    for (auto& s : c->extra.slots) {
+        s.pin.release(); s.dev.release(); cudaEventDestroy(s.done);
+        for (auto& t : s.t) cudaEventDestroy(t);
+    }
     for (auto& ev : c->ev) cudaEventDestroy(ev);
     cudaStreamDestroy(c->stream);
     delete c;
@@ -850,7 +902,7 @@ hb_status hb_eval_level(hb_ctx* c, hb_wires* w, const hb_gate* gates, uint32_t n
     }
     CU(c, cudaEventRecord(slot->t[2], c->stream));
     slot->first_is_pbs = p.order == 0; slot->pending = true;
-    if (hb_status s = launch_lin(c, w->dev, wstride, dl, (uint32_t)lj.size(), ct_words(c))) return s;
+    if (hb_status s = launch_lin(c, w->dev, wstride, dl, (uint32_t)lj.size(), ct_words(c), lin_hazard(lj))) return s;
     CU(c, cudaEventRecord(slot->done, c->stream));
     c->stats.levels++;
     return HB_OK;
@@ -900,7 +952,7 @@ hb_status hb_eval_shortint_ops(hb_ctx* c, hb_wires* w, const hb_sop* ops, uint32
     }
     if (!lin.empty()) {
         if (hb_status s = upload_jobs(c, {}, lin, {}, &dp, &dk, &dl, &slot)) return s;
-        if (hb_status s = launch_lincomb(c, w->dev, wstride, dk, (uint32_t)lin.size(), ct_words(c))) return s;
+        if (hb_status s = launch_lincomb(c, w->dev, wstride, dk, (uint32_t)lin.size(), ct_words(c), lincomb_hazard(lin))) return s;
         CU(c, cudaEventRecord(slot->done, c->stream));
     }
     c->stats.levels++;

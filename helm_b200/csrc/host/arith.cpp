@@ -334,9 +334,11 @@ static unsigned __int128 scalar_of(const std::string& w) {
 
 // One cell -> block program (dispatch of circuit.rs:1326-1431: a numeric operand selects the *_plain form, which is
 // always "ciphertext op scalar" whatever the operand order in the netlist)
-void ArithCircuit::build_gate(RadixBuilder& rb, RadixProgram& p, const EncWireMap& enc, const Gate& g) const {
+void ArithCircuit::build_gate(RadixBuilder& rb, RadixProgram& p, const RowOf& row_of, const Gate& g) const {
+    auto base_row = [&](const RowOf&, const std::string& w) { return row_of(w); };
+    const RowOf& enc = row_of;
     const uint32_t out = base_row(enc, g.output);
-    if (g.type == GateType::Copy) { rb.copy(p, base_row(enc, g.inputs.at(0)), out); return; }
+    if (g.type == GateType::Dff || g.type == GateType::Buf || g.type == GateType::Copy) { rb.copy(p, base_row(enc, g.inputs.at(0)), out); return; }
     if (!is_arith_type(g.type)) throw Error(std::string("gate type \"") + gate_type_name(g.type) + "\" cannot be evaluated in arithmetic mode");
     if (g.inputs.size() < 2) throw Error("arithmetic cell " + g.name + " needs two operands");
     const bool c0 = circuit_.is_constant_operand(g.inputs[0]), c1 = circuit_.is_constant_operand(g.inputs[1]);
@@ -377,23 +379,24 @@ std::unique_ptr<EncWireMap> ArithCircuit::encrypt_inputs(const std::set<std::str
     std::set<std::string> uniq(names.begin(), names.end());
     named_ = (uint32_t)uniq.size();
     scratch_first_ = named_ * (uint32_t)nb_;
-    // dry run over every level to size the scratch area (row numbers of named wires do not matter for the count)
+    // size the scratch area by building every level's programs (and the READY-latching ones) for real against an unbounded
+    // allocator: the row numbers of the named wires are those the wire map will assign (first occurrence in `names`)
     uint32_t need = 0;
     {
-        EncWireMap* none = nullptr; (void)none;
-        std::unordered_map<std::string, uint32_t> fake;
+        std::unordered_map<std::string, uint32_t> index;
+        for (const auto& n : names) if (!index.count(n)) { const uint32_t i = (uint32_t)index.size(); index[n] = i; }
+        const RowOf row_of = [&](const std::string& w) {
+            auto it = index.find(w);
+            if (it == index.end()) throw Error("wire \"" + w + "\" is not in the encrypted wire map");
+            return it->second * (uint32_t)nb_;
+        };
+        RadixBuilder rb(4, 4, nb_, scratch_first_, 0x40000000u);
         for (const auto& level : circuit_.levels()) {
-            uint32_t used = 0;
-            for (const Gate& g : level) {
-                const int terms = nb_ * (nb_ + 1);                             // partial products of one multiplication
-                if (g.type == GateType::Mult) used += (uint32_t)(4 * terms + 16 * nb_);
-                else if (g.type == GateType::Div) used += (uint32_t)(2 * nb_) * (uint32_t)(16 * nb_) + (uint32_t)(4 * nb_);   // bits x (shift, subtract, select)
-                else if (g.type == GateType::Shl || g.type == GateType::Shr) used += (uint32_t)(64 * nb_);
-                else used += (uint32_t)(16 * nb_);
-            }
-            need = std::max(need, used);
+            rb.reset_scratch();
+            for (const Gate& g : level) { RadixProgram p; build_gate(rb, p, row_of, g); }
+            need = std::max(need, rb.scratch_used());
         }
-        need = std::max<uint32_t>(need, (uint32_t)(3 * (4 * nb_ * (nb_ + 1) + 16 * nb_)) * (uint32_t)std::max<size_t>(1, nl.outputs.size()));
+        if (index.count("READY")) need = std::max(need, build_ready(rb, row_of, nullptr));
     }
     scratch_rows_ = need;
     auto enc = std::make_unique<EncWireMap>(sk_, names, scratch_first_ + scratch_rows_ - named_);
@@ -452,9 +455,7 @@ EncWireMap& ArithCircuit::evaluate_encrypted(EncWireMap& enc, size_t /*cycle*/, 
         rb.reset_scratch();
         std::vector<RadixProgram> progs(levels[li].size());
         for (size_t gi = 0; gi < levels[li].size(); ++gi) {
-            const Gate& g = levels[li][gi];
-            if (g.type == GateType::Dff || g.type == GateType::Buf) rb.copy(progs[gi], base_row(enc, g.inputs.at(0)), base_row(enc, g.output));
-            else build_gate(rb, progs[gi], enc, g);
+            build_gate(rb, progs[gi], [&](const std::string& w) { return base_row(enc, w); }, levels[li][gi]);
         }
         run(enc, progs);
         if (!quiet) {
@@ -477,28 +478,35 @@ void ArithCircuit::init_ready(EncWireMap& enc) {
     enc.set_trivial({base_row(enc, "__helm_one")}, ck_.delta());
 }
 
-// valid = wire * READY + valid * (1 - READY) for every output (circuit.rs:1209-1297)
-void ArithCircuit::evaluate_ready(EncWireMap& enc) {
+// valid = wire * READY + valid * (1 - READY) for every output (circuit.rs:1209-1297): three lock-step phases.
+// Returns the largest scratch use of a phase; with phases == nullptr it only measures.
+uint32_t ArithCircuit::build_ready(RadixBuilder& rb, const RowOf& row, std::vector<std::vector<RadixProgram>>* phases) const {
     const auto& outs = circuit_.netlist().outputs;
-    RadixBuilder rb(4, 4, nb_, scratch_first_, scratch_rows_);
-    const uint32_t ready = base_row(enc, "READY"), one = base_row(enc, "__helm_one"), nr = base_row(enc, "__helm_not_ready");
-    {
-        std::vector<RadixProgram> progs(1);
-        rb.sub(progs[0], one, ready, nr);
-        run(enc, progs);
-    }
+    const uint32_t ready = row("READY"), one = row("__helm_one"), nr = row("__helm_not_ready");
+    uint32_t need = 0;
+    std::vector<RadixProgram> sub(1), mul(2 * outs.size()), add(outs.size());
     rb.reset_scratch();
-    std::vector<RadixProgram> mul(2 * outs.size());
+    rb.sub(sub[0], one, ready, nr);
+    need = std::max(need, rb.scratch_used());
+    rb.reset_scratch();
     for (size_t o = 0; o < outs.size(); ++o) {
-        rb.mul(mul[2 * o], base_row(enc, outs[o]), ready, base_row(enc, "__helm_t1_" + outs[o]));
-        rb.mul(mul[2 * o + 1], base_row(enc, "__helm_valid_" + outs[o]), nr, base_row(enc, "__helm_t2_" + outs[o]));
+        rb.mul(mul[2 * o], row(outs[o]), ready, row("__helm_t1_" + outs[o]));
+        rb.mul(mul[2 * o + 1], row("__helm_valid_" + outs[o]), nr, row("__helm_t2_" + outs[o]));
     }
-    run(enc, mul);
+    need = std::max(need, rb.scratch_used());
     rb.reset_scratch();
-    std::vector<RadixProgram> add(outs.size());
     for (size_t o = 0; o < outs.size(); ++o)
-        rb.add(add[o], base_row(enc, "__helm_t1_" + outs[o]), base_row(enc, "__helm_t2_" + outs[o]), base_row(enc, "__helm_valid_" + outs[o]));
-    run(enc, add);
+        rb.add(add[o], row("__helm_t1_" + outs[o]), row("__helm_t2_" + outs[o]), row("__helm_valid_" + outs[o]));
+    need = std::max(need, rb.scratch_used());
+    if (phases) { phases->clear(); phases->push_back(std::move(sub)); phases->push_back(std::move(mul)); phases->push_back(std::move(add)); }
+    return need;
+}
+
+void ArithCircuit::evaluate_ready(EncWireMap& enc) {
+    RadixBuilder rb(4, 4, nb_, scratch_first_, scratch_rows_);
+    std::vector<std::vector<RadixProgram>> phases;
+    build_ready(rb, [&](const std::string& w) { return base_row(enc, w); }, &phases);
+    for (auto& ph : phases) run(enc, ph);
     ck_status(sk_.ctx(), hb_sync(sk_.ctx()), "hb_sync");
 }
 

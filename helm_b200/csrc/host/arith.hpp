@@ -19,6 +19,7 @@
 //   div                    : restoring long division (shift-in, subtract with carry-out, select), ct / ct and ct / scalar
 //   shl / shr by ciphertext: barrel shifter, one select per bit of the amount
 #pragma once
+#include <functional>
 #include "eval.hpp"
 
 namespace helm {
@@ -101,7 +102,9 @@ public:
     uint64_t batches() const { return n_batches_; }
 private:
     uint32_t base_row(const EncWireMap& enc, const std::string& wire) const { return enc.at(wire) * (uint32_t)nb_; }
-    void build_gate(RadixBuilder& rb, RadixProgram& p, const EncWireMap& enc, const Gate& g) const;
+    using RowOf = std::function<uint32_t(const std::string&)>;               // wire name -> first block row
+    void build_gate(RadixBuilder& rb, RadixProgram& p, const RowOf& row_of, const Gate& g) const;
+    uint32_t build_ready(RadixBuilder& rb, const RowOf& row_of, std::vector<std::vector<RadixProgram>>* phases) const;
     void run(EncWireMap& enc, std::vector<RadixProgram>& progs);
     void encrypt_value(unsigned __int128 v, uint8_t* dst) const;
     const ClientKey& ck_;

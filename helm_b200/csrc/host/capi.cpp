@@ -91,6 +91,15 @@ int64_t hh_circuit_level_width(const hh_circuit* c, int li) {
     const auto& lv = c->c->levels();
     return li < 0 || (size_t)li >= lv.size() ? -1 : (int64_t)lv[li].size();
 }
+int hh_circuit_names(const hh_circuit* c, int what, char* buf, size_t cap, size_t* needed) {
+    std::string s;
+    return guarded([&] {
+        const Netlist& nl = c->c->netlist();
+        const std::vector<std::string>* v = what == 2 ? &nl.inputs : what == 3 ? &nl.outputs : what == 4 ? &nl.dff_outputs : nullptr;
+        if (!v) throw Error("hh_circuit_names: what must be 2 (inputs), 3 (outputs) or 4 (dff_outputs)");
+        for (const auto& w : *v) s += w + "\n";
+    }) || emit(s, buf, cap, needed);
+}
 int hh_circuit_describe(const hh_circuit* c, char* buf, size_t cap, size_t* needed) {
     std::string s;
     return guarded([&] {
@@ -127,6 +136,8 @@ int hh_preprocess_assign_dict(const char* yosys_text, int arith, char* buf, size
     std::string s;
     return guarded([&] { s = preprocess_assign_dict(yosys_text ? yosys_text : "", arith != 0); }) || emit(s, buf, cap, needed);
 }
+
+void hh_chacha20_block(const uint32_t* key8, const uint32_t* w12_15, uint32_t* out16) { chacha20_block(key8, w12_15, out16); }
 
 int hh_read_input_csv(const char* path, const char* ptxt_type, char* buf, size_t cap, size_t* needed) {
     std::string s;

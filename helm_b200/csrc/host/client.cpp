@@ -1,6 +1,7 @@
 // See client.hpp.  LWE / GLWE / GGSW objects as in SURVEY.md App. A.2 (tfhe-rs 0.4.x conventions).
 #include "client.hpp"
 #include <cmath>
+#include <sys/random.h>
 #include <cstring>
 #include <map>
 #include "netlist.hpp"   // helm::Error
@@ -38,20 +39,60 @@ const Params& params_by_name(const std::string& name) {
     return it->second;
 }
 
-// ---------------------------------------------------------------- RNG (xoshiro256**, splitmix64 seeding)
+// ---------------------------------------------------------------- RNG: ChaCha20 keystream (RFC 8439 block function)
+// Every random word the client emits -- secret keys, public LWE / GLWE masks, Gaussian noise -- is ChaCha20 output, so
+// seeing masks (they are written into ciphertexts in the clear) reveals nothing about the noise or the keys.  The key is
+// 32 bytes from getrandom(2) (Rng::from_os, what hh_session_create uses for seed 0), or is expanded from a 64-bit seed for
+// reproducible tests and benchmarks (a 64-bit seed is not a production key: see client.hpp).  `stream` selects an
+// independent keystream (nonce word) so that masks and noise never share one.
 static uint64_t splitmix(uint64_t& x) {
     uint64_t z = (x += 0x9E3779B97F4A7C15ull);
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
     z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
     return z ^ (z >> 31);
 }
-Rng::Rng(uint64_t seed) { for (auto& v : s) v = splitmix(seed); }
-uint64_t Rng::next() {
-    auto rotl = [](uint64_t x, int k) { return (x << k) | (x >> (64 - k)); };
-    const uint64_t r = rotl(s[1] * 5, 7) * 9, t = s[1] << 17;
-    s[2] ^= s[0]; s[3] ^= s[1]; s[1] ^= s[2]; s[0] ^= s[3]; s[2] ^= t; s[3] = rotl(s[3], 45);
+Rng::Rng(uint64_t seed, uint32_t stream) {
+    for (int i = 0; i < 4; ++i) { const uint64_t v = splitmix(seed); key[2 * i] = (uint32_t)v; key[2 * i + 1] = (uint32_t)(v >> 32); }
+    nonce = stream;
+}
+Rng Rng::from_os(uint32_t stream) {
+    Rng r(0, stream);
+    size_t got = 0;
+    while (got < sizeof r.key) {
+        const ssize_t n = getrandom((char*)r.key + got, sizeof r.key - got, 0);
+        if (n <= 0) throw Error("getrandom failed: no OS entropy for the client keys");
+        got += (size_t)n;
+    }
     return r;
 }
+Rng Rng::fork(uint32_t stream) const { Rng r = *this; r.nonce = stream; r.counter = 0; r.have = 0; return r; }
+// out = ChaCha20 block function of key / words 12..15 (RFC 8439 section 2.3; known-answer test in tests/test_host_cpu.py)
+void chacha20_block(const uint32_t key[8], const uint32_t w12_15[4], uint32_t out[16]) {
+    static const uint32_t sigma[4] = {0x61707865u, 0x3320646eu, 0x79622d32u, 0x6b206574u};
+    uint32_t st[16], x[16];
+    for (int i = 0; i < 4; ++i) st[i] = sigma[i];
+    for (int i = 0; i < 8; ++i) st[4 + i] = key[i];
+    for (int i = 0; i < 4; ++i) st[12 + i] = w12_15[i];
+    for (int i = 0; i < 16; ++i) x[i] = st[i];
+    auto rotl = [](uint32_t v, int k) { return (v << k) | (v >> (32 - k)); };
+    auto qr = [&](int a, int b, int c, int d) {
+        x[a] += x[b]; x[d] = rotl(x[d] ^ x[a], 16); x[c] += x[d]; x[b] = rotl(x[b] ^ x[c], 12);
+        x[a] += x[b]; x[d] = rotl(x[d] ^ x[a], 8);  x[c] += x[d]; x[b] = rotl(x[b] ^ x[c], 7);
+    };
+    for (int round = 0; round < 10; ++round) {
+        qr(0, 4, 8, 12); qr(1, 5, 9, 13); qr(2, 6, 10, 14); qr(3, 7, 11, 15);
+        qr(0, 5, 10, 15); qr(1, 6, 11, 12); qr(2, 7, 8, 13); qr(3, 4, 9, 14);
+    }
+    for (int i = 0; i < 16; ++i) out[i] = x[i] + st[i];
+}
+void Rng::refill() {
+    const uint32_t w[4] = {(uint32_t)counter, (uint32_t)(counter >> 32), nonce, 0x48454C4Du};
+    uint32_t o[16];
+    chacha20_block(key, w, o);
+    for (int i = 0; i < 8; ++i) buf[i] = (uint64_t)o[2 * i] | ((uint64_t)o[2 * i + 1] << 32);
+    ++counter; have = 8;
+}
+uint64_t Rng::next() { if (!have) refill(); return buf[--have]; }
 double Rng::gauss() {
     const double u = ((next() >> 11) + 0.5) * (1.0 / 9007199254740992.0), v = ((next() >> 11) + 0.5) * (1.0 / 9007199254740992.0);
     return std::sqrt(-2.0 * std::log(u)) * std::cos(6.283185307179586476925 * v);
@@ -62,9 +103,9 @@ template <class T> static T torus_noise(Rng& r, double std) {
     return (T)(typename std::make_signed<T>::type)std::llround(x);
 }
 
-template <class T> static void lwe_encrypt_t(const uint8_t* sk, int dim, T pt, double std, Rng& r, T* ct) {
-    T b = pt + torus_noise<T>(r, std);
-    for (int i = 0; i < dim; ++i) { const T a = (T)r.next(); ct[i] = a; if (sk[i]) b += a; }
+template <class T> static void lwe_encrypt_t(const uint8_t* sk, int dim, T pt, double std, Rng& mask, Rng& noise, T* ct) {
+    T b = pt + torus_noise<T>(noise, std);
+    for (int i = 0; i < dim; ++i) { const T a = (T)mask.next(); ct[i] = a; if (sk[i]) b += a; }
     ct[dim] = b;
 }
 
@@ -72,7 +113,8 @@ ClientKey ClientKey::from_raw(const Params& p, const uint8_t* lwe_sk, const uint
     ClientKey ck; ck.p = p;
     ck.lwe_sk.assign(lwe_sk, lwe_sk + p.small_dim());
     ck.glwe_sk.assign(glwe_sk, glwe_sk + p.big_dim());
-    ck.rng = Rng(enc_seed);
+    const Rng base = enc_seed ? Rng(enc_seed, 0) : Rng::from_os(0);
+    ck.rng_mask = base.fork(1); ck.rng_noise = base.fork(2);
     return ck;
 }
 
@@ -80,8 +122,8 @@ void ClientKey::encrypt_raw(bool big, uint64_t pt, void* ct) const {
     const int dim = big ? p.big_dim() : p.small_dim();
     const uint8_t* sk = big ? glwe_sk.data() : lwe_sk.data();
     const double std = big ? p.glwe_std : p.lwe_std;
-    if (p.hb.torus_bits == 32) lwe_encrypt_t<uint32_t>(sk, dim, (uint32_t)pt, std, rng, (uint32_t*)ct);
-    else lwe_encrypt_t<uint64_t>(sk, dim, pt, std, rng, (uint64_t*)ct);
+    if (p.hb.torus_bits == 32) lwe_encrypt_t<uint32_t>(sk, dim, (uint32_t)pt, std, rng_mask, rng_noise, (uint32_t*)ct);
+    else lwe_encrypt_t<uint64_t>(sk, dim, pt, std, rng_mask, rng_noise, (uint64_t*)ct);
 }
 
 uint64_t ClientKey::phase(bool big, const void* ct) const {
@@ -124,7 +166,7 @@ template <class T> static void poly_mul_binary_acc(const T* a, const uint8_t* s,
     }
 }
 
-template <class T> static void gen_server_keys_t(const ClientKey& ck, uint64_t seed, ServerKeyMaterial* sk) {
+template <class T> static void gen_server_keys_t(const ClientKey& ck, const Rng& base, ServerKeyMaterial* sk) {
     const Params& p = ck.p;
     const int n = p.hb.n, k = p.hb.k, N = p.hb.N, l = p.hb.pbs_level, lk = p.hb.ks_level, BITS = (int)sizeof(T) * 8;
     const size_t row_words = (size_t)(k + 1) * N;
@@ -133,12 +175,12 @@ template <class T> static void gen_server_keys_t(const ClientKey& ck, uint64_t s
     // BSK_i = GGSW(s_i): for level lev and row r, a GLWE encryption of 0 plus s_i * q/B^lev on component r (App. A.2)
 #pragma omp parallel for schedule(dynamic, 4)
     for (int i = 0; i < n; ++i) {
-        Rng r(seed ^ (0x9E3779B97F4A7C15ull * (uint64_t)(i + 1)));
+        Rng r = base.fork(0x10000u + 2u * (uint32_t)i), rn = base.fork(0x10001u + 2u * (uint32_t)i);   // masks, noise
         for (int lev = 1; lev <= l; ++lev)
             for (int row = 0; row <= k; ++row) {
                 T* g = bsk + (((size_t)i * l + (lev - 1)) * (k + 1) + row) * row_words;
                 T* body = g + (size_t)k * N;
-                for (int c = 0; c < N; ++c) body[c] = torus_noise<T>(r, p.glwe_std);
+                for (int c = 0; c < N; ++c) body[c] = torus_noise<T>(rn, p.glwe_std);
                 for (int j = 0; j < k; ++j) {
                     T* a = g + (size_t)j * N;
                     for (int c = 0; c < N; ++c) a[c] = (T)r.next();
@@ -153,24 +195,25 @@ template <class T> static void gen_server_keys_t(const ClientKey& ck, uint64_t s
     T* ksk = (T*)sk->ksk.data();
 #pragma omp parallel for schedule(dynamic, 16)
     for (int i = 0; i < kN; ++i) {
-        Rng r(seed * 0x2545F4914F6CDD1Dull + 0xD1B54A32D192ED03ull * (uint64_t)(i + 1));
+        Rng r = base.fork(0x1000000u + 2u * (uint32_t)i), rn = base.fork(0x1000001u + 2u * (uint32_t)i);
         for (int lev = 1; lev <= lk; ++lev) {
             const T pt = ck.glwe_sk[i] ? ((T)1) << (BITS - p.hb.ks_base_log * lev) : (T)0;
-            lwe_encrypt_t<T>(ck.lwe_sk.data(), n, pt, p.lwe_std, r, ksk + ((size_t)i * lk + (lev - 1)) * (n + 1));
+            lwe_encrypt_t<T>(ck.lwe_sk.data(), n, pt, p.lwe_std, r, rn, ksk + ((size_t)i * lk + (lev - 1)) * (n + 1));
         }
     }
 }
 
 void gen_keys(const Params& p, uint64_t seed, ClientKey* ck, ServerKeyMaterial* sk) {
     if (p.hb.torus_bits != 32 && p.hb.torus_bits != 64) throw Error("torus_bits must be 32 or 64");
-    Rng r(seed);
+    // seed 0: key the generator from the OS (production); any other seed: reproducible keys for tests and benchmarks
+    const Rng base = seed ? Rng(seed, 0) : Rng::from_os(0);
+    Rng r = base.fork(3);                                    // secret-key stream
     ck->p = p;
     ck->lwe_sk.resize(p.small_dim()); ck->glwe_sk.resize(p.big_dim());
     for (auto& b : ck->lwe_sk) b = r.next() & 1;
     for (auto& b : ck->glwe_sk) b = r.next() & 1;
-    ck->rng = Rng(r.next());
-    const uint64_t ks = r.next();
-    if (sk) { if (p.hb.torus_bits == 32) gen_server_keys_t<uint32_t>(*ck, ks, sk); else gen_server_keys_t<uint64_t>(*ck, ks, sk); }
+    ck->rng_mask = base.fork(1); ck->rng_noise = base.fork(2);
+    if (sk) { if (p.hb.torus_bits == 32) gen_server_keys_t<uint32_t>(*ck, base, sk); else gen_server_keys_t<uint64_t>(*ck, base, sk); }
 }
 
 }  // namespace helm

@@ -6,8 +6,10 @@
 // hb_load_bsk / hb_load_ksk; this file exists so that the C++ harness and CLI are self-contained.
 // The GPU engine never sees anything declared here except the two server-key arrays.
 //
-// NOTE: the generator is xoshiro256** (statistical quality, reproducible from a seed) -- fine for benchmarks and
-// tests, NOT a CSPRNG.  Production keys come from the caller (ClientKey::from_raw / hh_keys_from_raw).
+// Randomness: every key bit, public mask word and noise sample is ChaCha20 keystream (client.cpp), masks and noise on
+// separate streams.  With seed 0 (gen_keys / from_raw / hh_session_create) the 256-bit ChaCha key comes from getrandom(2):
+// that is the production setting.  A non-zero seed expands 64 bits into the key so that tests and benchmarks are
+// reproducible -- 64 bits of entropy, TEST / BENCH USE ONLY.
 #pragma once
 #include <cstdint>
 #include <string>
@@ -29,11 +31,18 @@ struct Params {
 // and the small "toy32"/"toy64"/"toy64b" sets used by fast tests.  Values: SURVEY.md section 8 / App. A.1.
 const Params& params_by_name(const std::string& name);
 
+void chacha20_block(const uint32_t key[8], const uint32_t w12_15[4], uint32_t out[16]);
+
 struct Rng {
-    uint64_t s[4];
-    explicit Rng(uint64_t seed);
+    uint32_t key[8]; uint32_t nonce = 0; uint64_t counter = 0;
+    uint64_t buf[8]; int have = 0;
+    explicit Rng(uint64_t seed = 0, uint32_t stream = 0);   // test / bench: key expanded from a 64-bit seed
+    static Rng from_os(uint32_t stream);                     // production: key from getrandom(2)
+    Rng fork(uint32_t stream) const;                         // same key, independent keystream
     uint64_t next();
     double gauss();
+private:
+    void refill();
 };
 
 struct ServerKeyMaterial {                 // standard-domain keys in the layouts hb_load_bsk / hb_load_ksk take
@@ -45,7 +54,7 @@ class ClientKey {
 public:
     Params p;
     std::vector<uint8_t> lwe_sk, glwe_sk;  // binary; glwe_sk flattened (kN)
-    mutable Rng rng{0};
+    mutable Rng rng_mask{0, 1}, rng_noise{0, 2};   // public masks / secret noise: separate ChaCha20 streams
 
     static ClientKey from_raw(const Params& p, const uint8_t* lwe_sk, const uint8_t* glwe_sk, uint64_t enc_seed);
     // torus plaintext -> ciphertext words (dim+1) under the small (big = false) or big key

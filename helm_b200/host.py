@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libhelm_host.so")
 EXPORTS = ["hh_last_error", "hh_circuit_load", "hh_circuit_load_text", "hh_circuit_free", "hh_circuit_count",
-           "hh_circuit_level_width", "hh_circuit_describe", "hh_circuit_eval_plain", "hh_read_input_csv", "hh_preprocess_yosys", "hh_preprocess_yosys_mode", "hh_preprocess_assign_dict",
+           "hh_circuit_level_width", "hh_circuit_names", "hh_circuit_describe", "hh_circuit_eval_plain", "hh_read_input_csv", "hh_chacha20_block", "hh_preprocess_yosys", "hh_preprocess_yosys_mode", "hh_preprocess_assign_dict",
            "hh_session_create", "hh_session_free", "hh_session_run", "hh_session_run_arith", "hh_session_stats"]
 _LIB = None
 
@@ -35,11 +35,14 @@ def lib():
         L.hh_circuit_level_width.restype = C.c_int64
         L.hh_circuit_level_width.argtypes = [vp, C.c_int]
         L.hh_circuit_describe.argtypes = [vp, vp, sz, C.POINTER(sz)]
+        L.hh_circuit_names.argtypes = [vp, C.c_int, vp, sz, C.POINTER(sz)]
         L.hh_circuit_eval_plain.argtypes = [vp, cp, cp, C.c_int, vp, sz, C.POINTER(sz)]
         L.hh_read_input_csv.argtypes = [cp, cp, vp, sz, C.POINTER(sz)]
         L.hh_preprocess_yosys.argtypes = [cp, vp, sz, C.POINTER(sz)]
         L.hh_preprocess_yosys_mode.argtypes = [cp, C.c_int, vp, sz, C.POINTER(sz)]
         L.hh_preprocess_assign_dict.argtypes = [cp, C.c_int, vp, sz, C.POINTER(sz)]
+        L.hh_chacha20_block.argtypes = [vp, vp, vp]
+        L.hh_chacha20_block.restype = None
         L.hh_session_create.argtypes = [cp, C.c_int, C.c_uint64, vp, vp, vp, sz, vp, sz, C.POINTER(vp)]
         L.hh_session_free.argtypes = [vp]
         L.hh_session_run.argtypes = [vp, vp, cp, C.c_int, C.c_int, C.c_int, vp, sz, C.POINTER(sz), C.POINTER(C.c_double)]
@@ -128,6 +131,11 @@ class Circuit:
 
     def level_widths(self):
         return [int(self.L.hh_circuit_level_width(self.h, i)) for i in range(self.count(self.LEVELS))]
+
+    def names(self, what):
+        """Declared INPUTS (DFF outputs appended, as the reference's parser does), OUTPUTS or DFFS, in file order, unique."""
+        txt = _text(lambda b, c, n: self.L.hh_circuit_names(self.h, what, b, c, n))
+        return list(dict.fromkeys(x for x in txt.splitlines() if x))
 
     def inputs(self):
         """Wires read by some gate and driven by none (primary inputs actually used)."""

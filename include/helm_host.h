@@ -27,6 +27,8 @@ void hh_circuit_free(hh_circuit*);
  * (DFF level included), 6 has_luts, 7 has_arith, 8 bootstrapped gates (PBS gates; MUX counts once) */
 int64_t hh_circuit_count(const hh_circuit*, int what);
 int64_t hh_circuit_level_width(const hh_circuit*, int level_index);
+/* one name per line: what = 2 declared inputs (duplicates kept, DFF outputs appended), 3 outputs, 4 dff_outputs */
+int hh_circuit_names(const hh_circuit*, int what, char* buf, size_t cap, size_t* needed);
 /* "level:type:name:out:in0,in1,...\n" per gate in level order */
 int hh_circuit_describe(const hh_circuit*, char* buf, size_t cap, size_t* needed);
 /* plaintext evaluation: inputs as "wire=value\n" lines (empty => all false/0); ptxt_type "bool" | "u8".."u128";
@@ -48,8 +50,14 @@ int hh_preprocess_assign_dict(const char* yosys_text, int arith, char* buf, size
 /* CSV helper (reference read_input_wires): file -> "wire=value\n" lines */
 int hh_read_input_csv(const char* path, const char* ptxt_type, char* buf, size_t cap, size_t* needed);
 
-/* encrypted evaluation on the GPU engine.  Keys: generated here from a seed (raw pointers NULL), or supplied by the
- * caller (tfhe-rs in the drop-in; the oracle in tests): lwe_sk n bytes, glwe_sk kN bytes, bsk/ksk standard domain. */
+/* the ChaCha20 block function (RFC 8439 2.3) behind every random word of the client side (keys, masks, noise): exported
+ * for its known-answer test.  key8: 8 words, w12_15: counter / nonce words 12..15, out16: 16 keystream words. */
+void hh_chacha20_block(const uint32_t* key8, const uint32_t* w12_15, uint32_t* out16);
+
+/* encrypted evaluation on the GPU engine.  Keys: generated here (raw pointers NULL), or supplied by the caller (tfhe-rs in
+ * the drop-in; the oracle in tests): lwe_sk n bytes, glwe_sk kN bytes, bsk/ksk standard domain.
+ * seed == 0: the client generator (ChaCha20; secret keys, masks and noise of keys and input ciphertexts) is keyed with 256
+ * bits from getrandom(2) -- the production setting.  seed != 0: reproducible keys from 64 bits, tests and benchmarks only. */
 int hh_session_create(const char* param_set, int device, uint64_t seed,
                       const uint8_t* lwe_sk, const uint8_t* glwe_sk, const void* bsk, size_t bsk_bytes,
                       const void* ksk, size_t ksk_bytes, hh_session** out);

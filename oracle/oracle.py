@@ -90,10 +90,17 @@ def lib():
         L.orc_bool_linear.argtypes = [vp, C.c_int, vp, vp, vp]
         L.orc_shortint_accumulator.argtypes = [vp, vp, vp]
         L.orc_shortint_lut.argtypes = [vp, vp, vp, vp, C.c_int]
+        L.orc_set_threads.restype = C.c_int
+        L.orc_set_threads.argtypes = [C.c_int]
         L.orc_bool_level.restype = C.c_int
         L.orc_bool_level.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_uint32, C.c_int]
         _LIB = L
     return _LIB
+
+
+def set_threads(n=0):
+    """OpenMP team of the batched calls (0: every online core, whatever OMP_NUM_THREADS says); returns the team size."""
+    return int(lib().orc_set_threads(n))
 
 
 def _p(a):

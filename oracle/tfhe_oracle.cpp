@@ -559,6 +559,18 @@ void orc_shortint_lut(const orc_keys* K, const void* in, const uint64_t* table, 
     }
 }
 
+// OpenMP team size of the batched entry points.  torch.distributed.run exports OMP_NUM_THREADS=1 to its workers; the CPU arm
+// of bench.py (rank 0 alone) sets the team explicitly.  n <= 0: all online cores.  Returns the team size now in effect.
+int orc_set_threads(int n) {
+#ifdef _OPENMP
+    if (n <= 0) n = omp_get_num_procs();
+    omp_set_num_threads(n);
+    return omp_get_max_threads();
+#else
+    (void)n; return 1;
+#endif
+}
+
 int orc_bool_level(const orc_keys* K, void* wires, const uint8_t* ops, const uint32_t* in0, const uint32_t* in1,
                    const uint32_t* in2, const uint32_t* out, uint32_t count, int mode) {
     ensure_mode(K, mode);

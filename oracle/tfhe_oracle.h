@@ -93,6 +93,9 @@ void orc_shortint_accumulator(const orc_keys*, const uint64_t* table, void* test
 /* ct_out = PBS(KS(ct_in)) with accumulator from table */
 void orc_shortint_lut(const orc_keys*, const void* ct_in, const uint64_t* table, void* ct_out, int mode);
 
+/* OpenMP team size of orc_bool_level (n <= 0: all online cores); returns the size now in effect */
+int orc_set_threads(int n);
+
 /* batched CPU baseline: evaluates `count` independent boolean gates (OpenMP, one gate per thread).
  * wires: [n_wires][n+1]; gate g reads in0[g], in1[g] (and in2[g] for MUX), writes out[g]. returns #threads used */
 int orc_bool_level(const orc_keys*, void* wires, const uint8_t* ops, const uint32_t* in0, const uint32_t* in1,

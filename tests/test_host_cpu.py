@@ -132,3 +132,52 @@ def test_iscas85_shapes(name, levels, maxw, pbs_gates, mux):   # SURVEY.md App. 
     assert c.count(C.LEVELS) == levels and max(c.level_widths()) == maxw and c.count(C.PBS_GATES) == pbs_gates
     assert sum(1 for g in c.gates() if g[1] == "mux") == mux
     c.evaluate()                                        # all-false inputs evaluate without missing wires
+
+
+def test_client_rng_is_chacha20_known_answer():
+    """client randomness (keys, masks, noise) must come from a CSPRNG.  The generator is the ChaCha20 block
+    function; RFC 8439 section 2.3.2 test vector (key 00..1f, counter 1, nonce 00:00:00:09 00:00:00:4a 00:00:00:00)."""
+    import ctypes
+    import numpy as np
+    key = np.frombuffer(bytes(range(32)), dtype="<u4").copy()
+    w = np.array([1, 0x09000000, 0x4a000000, 0], dtype=np.uint32)
+    out = np.zeros(16, dtype=np.uint32)
+    H.lib().hh_chacha20_block(key.ctypes.data, w.ctypes.data, out.ctypes.data)
+    want = [0xe4e7f110, 0x15593bd1, 0x1fdd0f50, 0xc47120a3, 0xc7f4d1c7, 0x0368c033, 0x9aaa2204, 0x4e6cd4c3,
+            0x466482d2, 0x09aa9f07, 0x05d7c214, 0xa2028bd9, 0xd19c12b5, 0xb94e16de, 0xe883d0cb, 0x4e3c50a2]
+    assert [int(v) for v in out] == want
+
+
+def test_sequential_fixtures_plaintext():
+    """The sequential fixtures of tests/test_gpu_ready.py on the plaintext evaluator: a chain of DFFs is a shift register
+    (each DFF latches the pre-level value of its D wire), and the 2-bit counter raises READY in cycle 3 only."""
+    c = C(os.path.join(NET, "shift_register.v"))
+    assert c.count(C.DFFS) == 3 and c.level_widths() == [1, 3]
+    ins = {"d": False, "q1": False, "q2": False, "q3": False}
+    assert [c.evaluate(ins, cycles=k)["q3"] for k in (1, 2, 3, 4)] == [False, False, True, True]
+    for name in ("ready_gates.v", "ready_lut.v"):
+        r = C(os.path.join(NET, name))
+        ins = {"a": True, "b": False, "q0": False, "q1": False, "q2": False}
+        assert [r.evaluate(ins, cycles=k)["READY"] for k in (1, 2, 3, 4)] == [False, False, True, False]
+        assert r.evaluate(ins, cycles=3)["y"] is False and r.evaluate(ins, cycles=4)["y"] is False
+    a = C(os.path.join(NET, "ready_arith.v"), is_arith=True)
+    ins = {"x": 9, "cnt": 0, "acc": 0}
+    assert [(a.evaluate(ins, "u8", cycles=k)["READY"], a.evaluate(ins, "u8", cycles=k)["total"]) for k in (1, 2, 3, 4)] == \
+        [(0, 9), (0, 18), (1, 27), (1, 36)]
+
+
+def test_corpus_preprocesses_and_levelizes():
+    """Every Yosys netlist of the reference's corpus (tests/golden/yosys) goes through the restated preprocessor, levelizer and
+    plaintext evaluator; SURVEY App. B shapes for the ISCAS'85 gate netlists (HELM convention: NOT is a level)."""
+    import corpus
+    names = corpus.names()
+    assert len(names) >= 68
+    shapes = {"c432.v": (30, 148), "c499.v": (11, 200), "c880.v": (26, 262), "c1355.v": (11, 198), "c1908.v": (17, 157),
+              "c6288.v": (73, 1593), "16-bit-mult-gates.v": (31, 684)}
+    for name in names:
+        if name in corpus.REFERENCE_PANICS:
+            continue
+        c = C(text=H.preprocess_yosys(corpus.text(name), exact_consts=True))
+        assert c.count(C.LEVELS) >= 1 and c.evaluate()
+        if name in shapes:
+            assert (c.count(C.LEVELS), c.count(C.PBS_GATES)) == shapes[name], name
