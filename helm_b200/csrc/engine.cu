@@ -95,13 +95,24 @@ struct hb_ctx {
     hb_stats_t stats{};
     std::string err;
     int sm_count = 0;
+    // multi-device group (hb_ctx_create_multi): the group context owns one ordinary context per device and fans every call
+    // out; `level_ev` of a member = "my share of the current level is evaluated and pushed to every peer"
+    std::vector<hb_ctx*> subs;
+    cudaEvent_t level_ev = nullptr;
+    uint32_t shard_min = 0;                // gates per device below which a level is not split further
+    bool is_group() const { return !subs.empty(); }
 };
+
+constexpr int HB_MAX_DEV = 8;
+struct PushArgs { void* dst[HB_MAX_DEV]; int n_dst; };
 
 struct hb_wires {
     hb_ctx* ctx = nullptr;
     void* dev = nullptr;
     uint32_t n_wires = 0;
     bool owned = false;
+    std::vector<hb_wires*> subs;           // group wires: one replica per device, kept coherent level by level
+    PushArgs peers{};                      // member of a group: the other replicas (peer-mapped over NVLink)
 };
 
 namespace {
@@ -167,6 +178,22 @@ template <class T, int MODE> __global__ void lincomb_rows(T* w, uint32_t stride,
             for (int s = 0; s < 4; ++s) if (j.c[s]) v += (T)(int64_t)j.c[s] * w[(size_t)j.src[s] * stride + x];
             if (x == words - 1) v += (T)j.cst;
             d[x] = v;
+        }
+    }
+}
+
+// Level exchange of a multi-device group: every output row of this device's share of the level is stored into the
+// replicas of all peers over NVLink (peer-mapped memory, 16-byte stores, a row per blockIdx.y), right behind the kernels that
+// produced it on the same stream; a per-level event per device then orders the peers' next level after it.  The rows are
+// named by the `dst` field of the job descriptors that are already on the device.
+template <class J> __global__ void push_rows(const void* src, PushArgs P, uint32_t row_bytes, const J* jobs, uint32_t cnt) {
+    const uint32_t q = row_bytes >> 4;
+    for (uint32_t r = blockIdx.y; r < cnt; r += gridDim.y) {
+        const size_t off = (size_t)jobs[r].dst * row_bytes;
+        const uint4* s = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(src) + off);
+        for (uint32_t x = blockIdx.x * blockDim.x + threadIdx.x; x < q; x += gridDim.x * blockDim.x) {
+            const uint4 v = s[x];
+            for (int p = 0; p < P.n_dst; ++p) reinterpret_cast<uint4*>(reinterpret_cast<char*>(P.dst[p]) + off)[x] = v;
         }
     }
 }
@@ -475,6 +502,20 @@ hb_status launch_lincomb(hb_ctx* c, void* w, uint32_t stride, const KsJob* jobs,
     return c->p.torus_bits == 32 ? launch_lincomb_t<uint32_t>(c, w, stride, jobs, cnt, words, staged)
                                  : launch_lincomb_t<uint64_t>(c, w, stride, jobs, cnt, words, staged);
 }
+
+template <class J> hb_status launch_push(hb_ctx* c, hb_wires* w, const J* jobs, uint32_t cnt) {
+    if (!cnt || !w->peers.n_dst) return HB_OK;
+    const uint32_t row_bytes = (uint32_t)(pad4(ct_words(c)) * tsize(c));
+    const dim3 grid((row_bytes / 16 + 255) / 256, cnt < 32768 ? cnt : 32768);
+    push_rows<J><<<grid, 256, 0, c->stream>>>(w->dev, w->peers, row_bytes, jobs, cnt);
+    CU(c, cudaGetLastError());
+    c->stats.kernel_launches++;
+    c->stats.push_bytes += (uint64_t)cnt * row_bytes * (uint64_t)w->peers.n_dst;
+    return HB_OK;
+}
+
+// error text of a group member -> the group context
+hb_status lift(hb_ctx* g, hb_ctx* sub, hb_status s) { if (s != HB_OK) g->err = "device " + std::to_string(sub->device) + ": " + sub->err; return s; }
 
 }  // namespace
 

@@ -31,7 +31,8 @@ class HbGate(C.Structure):
 class HbStats(C.Structure):
     _fields_ = [("pbs_count", C.c_uint64), ("ks_count", C.c_uint64), ("levels", C.c_uint64),
                 ("pbs_ms", C.c_double), ("ks_ms", C.c_double), ("kernel_launches", C.c_uint64),
-                ("pbs_ms_total", C.c_double), ("ks_ms_total", C.c_double), ("gap_ms_total", C.c_double)]
+                ("pbs_ms_total", C.c_double), ("ks_ms_total", C.c_double), ("gap_ms_total", C.c_double),
+                ("push_bytes", C.c_uint64), ("n_devices", C.c_uint32), ("sharded_levels", C.c_uint32)]
 
 
 GATE_DTYPE = np.dtype([("op", np.uint8), ("arity", np.uint8), ("flags", np.uint16), ("in", np.uint32, (4,)),
@@ -43,7 +44,7 @@ SOP_DTYPE = np.dtype([("kind", np.uint8), ("n_in", np.uint8), ("coef", np.int8, 
                       ("in", np.uint32, (4,)), ("out", np.uint32), ("table", np.uint64)], align=True)
 assert SOP_DTYPE.itemsize == 40 and SOP_DTYPE.fields["in"][1] == 8 and SOP_DTYPE.fields["table"][1] == 32
 
-EXPORTS = ["hb_ctx_create", "hb_ctx_destroy", "hb_last_error", "hb_set_params", "hb_load_bsk", "hb_load_ksk",
+EXPORTS = ["hb_ctx_create", "hb_ctx_create_multi", "hb_ctx_destroy", "hb_last_error", "hb_set_params", "hb_load_bsk", "hb_load_ksk",
            "hb_wires_create", "hb_wires_attach", "hb_wires_destroy", "hb_ct_words", "hb_wire_stride",
            "hb_wires_device_ptr", "hb_wires_write", "hb_wires_read", "hb_wires_write_rows", "hb_wires_read_rows", "hb_wires_set_trivial", "hb_eval_level", "hb_eval_shortint_ops",
            "hb_sync", "hb_stats", "hb_stream", "hb_pbs_batch", "hb_keyswitch_batch", "hb_measure_fp64_peak"]
@@ -64,6 +65,7 @@ def lib():
         L = C.CDLL(LIB_PATH)
         vp, u32, i32 = C.c_void_p, C.c_uint32, C.c_int32
         L.hb_ctx_create.argtypes = [i32, C.POINTER(vp)]
+        L.hb_ctx_create_multi.argtypes = [C.POINTER(i32), i32, u32, C.POINTER(vp)]
         L.hb_ctx_destroy.argtypes = [vp]
         L.hb_last_error.restype = C.c_char_p
         L.hb_last_error.argtypes = [vp]
@@ -120,12 +122,18 @@ def make_gates(ops, in0, in1, out, in2=None, in3=None, lut=None, arity=None):
 
 
 class Engine:
-    """One context on one GPU: resident Fourier BSK + KSK, batched level evaluation."""
+    """One context on one GPU -- or, with devices=[...], on a group of GPUs of this node (hb_ctx_create_multi: keys and wires
+    replicated, wide levels sharded, outputs exchanged over NVLink inside the engine): resident Fourier BSK + KSK, batched
+    level evaluation."""
 
-    def __init__(self, params, device=0):
+    def __init__(self, params, device=0, devices=None, min_gates_per_device=0):
         self.L = lib()
         self.h = C.c_void_p()
-        st = self.L.hb_ctx_create(device, C.byref(self.h))
+        if devices is None:
+            st = self.L.hb_ctx_create(device, C.byref(self.h))
+        else:
+            arr = (C.c_int32 * len(devices))(*devices)
+            st = self.L.hb_ctx_create_multi(arr, len(devices), min_gates_per_device, C.byref(self.h))
         if st != HB_OK:
             raise EngineError("hb_ctx_create: %s" % self.L.hb_last_error(None).decode())
         keys = [f for f, _ in HbParams._fields_]

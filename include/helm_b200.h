@@ -17,8 +17,9 @@
  *   hb_pbs_batch / hb_keyswitch_batch   the two tfhe-rs primitives underneath
  *        (programmable_bootstrap_lwe_ciphertext, keyswitch_lwe_ciphertext).
  *
- * Threading: one hb_ctx is bound to one CUDA device and driven by one host thread at a time;
- * work is stream-ordered on the context's stream.  Host buffers are only read/written during the
+ * Threading: one hb_ctx is bound to one CUDA device (hb_ctx_create) or to a group of devices (hb_ctx_create_multi) and driven
+ * by one host thread at a time; work is stream-ordered on the context's stream(s).  Distinct contexts share no mutable state and
+ * may be driven from different threads, on the same or on different devices.  Host buffers are only read/written during the
  * call.  The engine never sees a secret key.
  * There is no CPU fallback: every compute entry point returns HB_ERR_CUDA when no device exists.
  */
@@ -65,9 +66,24 @@ typedef struct {
     uint64_t kernel_launches;           /* engine kernels launched since context creation */
     double pbs_ms_total, ks_ms_total;   /* device time summed over every hb_eval_level since creation */
     double gap_ms_total;                /* stream time between consecutive batches' kernels (job upload, launch gaps) */
+    uint64_t push_bytes;                /* multi-device contexts: bytes stored into peer replicas over NVLink (level exchange) */
+    uint32_t n_devices;                 /* 1, or the size of the hb_ctx_create_multi group */
+    uint32_t sharded_levels;            /* levels / batches that were split over more than one device */
 } hb_stats_t;
 
 hb_status hb_ctx_create(int32_t device, hb_ctx** out);
+/* One context over n_devices GPUs of this node (1 <= n <= 8, distinct, all peer-accessible: NVLink / NVSwitch).  The reference's
+ * own GPU backend owns its device handles inside the circuit object the same way (src/circuit.rs:81-91, 650-934).  Keys are
+ * replicated on every device (hb_load_bsk / hb_load_ksk load all of them), every hb_wires array has one replica per device, and
+ * hb_eval_level / hb_eval_shortint_ops split a wide batch into contiguous slices, one per device; each device stores its output
+ * rows straight into every peer's replica (peer-mapped stores right behind the producing kernels) and a per-level event per
+ * device orders the next level after the exchange -- no host round trip (the reference gathers every level through host memory,
+ * src/circuit.rs:745-761, 877-892) and no collective library.  Batches narrower than min_gates_per_device x 2 stay on the first
+ * device (its outputs are still pushed, so the replicas stay coherent).  min_gates_per_device = 0 picks the default (one gate per
+ * SM: a narrower slice cannot make a level faster).  Every other entry point takes the group context like an ordinary one;
+ * hb_wires_read* read the first replica, hb_wires_write* / hb_wires_set_trivial write all of them, hb_stream / hb_pbs_batch /
+ * hb_keyswitch_batch address the first device, hb_wires_attach is not supported. */
+hb_status hb_ctx_create_multi(const int32_t* devices, int32_t n_devices, uint32_t min_gates_per_device, hb_ctx** out);
 hb_status hb_ctx_destroy(hb_ctx*);
 const char* hb_last_error(const hb_ctx*);          /* ctx may be NULL: last creation error */
 hb_status hb_set_params(hb_ctx*, const hb_params*);
