@@ -209,12 +209,16 @@ def emit_line(line):
 
 
 def workload_config(args, n):
+    if getattr(args, "single_process", False) and args.gpus > 1:
+        n = args.gpus
     return {"workload": "synthetic levelized netlist, %d two-input gates/level, depth %d (BASELINE.json configs[4])"
                         % (args.width, DEPTH),
             "params": "tfhe boolean DEFAULT_PARAMETERS n=722 k=2 N=512 l=3 B=2^6 ks l=4 B=2^3 (u32 torus)",
             "step": "one level = one hb_eval_level batch of %d gate bootstraps (PBS + keyswitch each)" % args.width,
-            "sharding": "level sharded over %d GPU(s), keys replicated, NCCL all-gather of outputs per level" % n if n > 1
-                        else "single GPU",
+            "sharding": ("level sharded over %d GPU(s), keys replicated, %s" % (
+                            n, "one process: hb_ctx_create_multi, outputs stored into peer replicas over NVLink + per-level events"
+                            if getattr(args, "single_process", False) else "one rank per GPU, NCCL all-gather of outputs per level"))
+                        if n > 1 else "single GPU",
             "l2": "inputs larger than L2: each level reads/writes a different 190 MB block of the 6.3 GB wire array"}
 
 
@@ -298,6 +302,9 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-latency", action="store_true", help="skip the c7552 gates-mode latency leg")
+    ap.add_argument("--single-process", action="store_true",
+                    help="drive all --gpus devices from THIS process through hb_ctx_create_multi (level sharding and the NVLink "
+                         "exchange inside the engine) instead of one torchrun rank per GPU with NCCL")
     args = ap.parse_args()
     # the contract is ONE JSON line on stdout: libraries (NCCL prints its version banner there) get stderr instead
     global _REAL_STDOUT
@@ -317,6 +324,9 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    group = list(range(args.gpus)) if (args.single_process and args.gpus > 1) else None
+    if group:
+        assert world == 1, "--single-process is not launched under torchrun"
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- helm_b200 has no CPU fallback")
     torch.cuda.set_device(local)
@@ -330,12 +340,17 @@ def main():
     g0, Wr = shard.level_slice(W, world, rank)
 
     K = O.Keys(PARAM_SET, seed=3)
-    eng = helm_b200.Engine(K.params, device=local)
+    eng = helm_b200.Engine(K.params, device=local, devices=group)
     eng.load_keys(K.bsk(), K.ksk())
     stride, words = eng.stride, eng.ct_words
-    # device wire array: (DEPTH+1) level blocks of W rows; attached so torch/NCCL can address it
-    wt = torch.zeros(((DEPTH + 1) * W, stride), dtype=torch.int32, device="cuda")
-    wires = eng.wires((DEPTH + 1) * W, device_ptr=wt.data_ptr())
+    # device wire array: (DEPTH+1) level blocks of W rows; attached so torch/NCCL can address it (one engine-owned replica per
+    # device in --single-process mode)
+    if group:
+        wt = None
+        wires = eng.wires((DEPTH + 1) * W)
+    else:
+        wt = torch.zeros(((DEPTH + 1) * W, stride), dtype=torch.int32, device="cuda")
+        wires = eng.wires((DEPTH + 1) * W, device_ptr=wt.data_ptr())
     ext = torch.cuda.ExternalStream(eng.stream(), device=torch.device("cuda", local))
 
     bits0 = (splitmix64(2, W) & np.uint64(1)).astype(np.uint8)
@@ -460,7 +475,7 @@ def main():
 
     # ---- CPU baseline (rank 0, N = 1 only): bounded sample of level 1 on the host cores
     cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu:
+    if rank == 0 and world == 1 and not group and not args.no_cpu:
         threads = os.cpu_count() or 1
         sample = min(W, args.cpu_gates if args.cpu_gates else 384 * threads)                    # ~15 s of host work
         ops1, i0, i1 = synth_level(1, W)
@@ -480,7 +495,7 @@ def main():
     # ---- BASELINE.json metric, second half: c7552 gates-mode end-to-end latency (configs[1]) through the host library
     # (Yosys netlist -> restated preprocessor -> levelizer -> one hb_eval_level per level), N = 1 only
     c7552 = c7552_lut = None
-    if rank == 0 and world == 1 and not args.no_latency:
+    if rank == 0 and world == 1 and not group and not args.no_latency:
         c7552 = iscas_latency("c7552", local)
         if c7552 is not None and not args.no_cpu:
             c7552.update(iscas_cpu_latency("c7552"))
@@ -488,15 +503,15 @@ def main():
 
     if rank == 0:
         value = W * args.steps / (ms_total * 1e-3)
-        flops_per_launch = Wr * K.n * F_CMUX
+        flops_per_launch = (Wr // len(group) if group else Wr) * K.n * F_CMUX      # per device
         ach = flops_per_launch / (pbs_ms * 1e-3) / 1e12 if pbs_ms > 0 else None
         bsk_bytes = K.n * 9 * 3 * 256 * 16
-        traffic, traffic_src = ncu_traffic("pbs16_kernel", Wr) if world == 1 else (None, None)
+        traffic, traffic_src = ncu_traffic("pbs16_kernel", Wr) if (world == 1 and not group) else (None, None)
         # independent anchor for the in-run DFMA measurement: 64 FP64 lanes per SM x 2 flop x the SM clock sampled under load
         sm_count = torch.cuda.get_device_properties(local).multi_processor_count
         sm_mhz = (clocks or {}).get("sm_mhz") or 0.0
         peak_theory = sm_count * 64 * 2 * sm_mhz * 1e6 / 1e12 if sm_mhz else None
-        line = {"metric": "PBS/s (batched gate bootstraps)", "value": value, "unit": "PBS/s", "n_gpus": world,
+        line = {"metric": "PBS/s (batched gate bootstraps)", "value": value, "unit": "PBS/s", "n_gpus": len(group) if group else world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic", "config": workload_config(args, world),
@@ -513,6 +528,8 @@ def main():
                              "hbm_floor_ms": 1e3 * (bsk_bytes + 3.0 * Wr * words * 4) / (hbm_peak_gbs() * 1e9)},
                 "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
                 "verified": verified, "c7552_gates_mode": c7552, "c7552_lut_mode": c7552_lut}
+        if group:
+            line["multi"] = {k: st1[k] for k in ("n_devices", "sharded_levels", "push_bytes")}
         emit_line(line)
     wires.close()
     eng.close()

@@ -519,6 +519,16 @@ hb_status lift(hb_ctx* g, hb_ctx* sub, hb_status s) { if (s != HB_OK) g->err = "
 
 }  // namespace
 
+// ================================================================ multi-device group (implemented at the end of this file)
+namespace {
+hb_status group_destroy(hb_ctx* g);
+hb_status group_each(hb_ctx* g, hb_status (*f)(hb_ctx*, const void*, size_t), const void* a, size_t b);
+hb_status group_wires_create(hb_ctx* g, uint32_t n_wires, hb_wires** out);
+hb_status group_eval_level(hb_ctx* g, hb_wires* w, const hb_gate* gates, uint32_t n_gates);
+hb_status group_eval_sops(hb_ctx* g, hb_wires* w, const hb_sop* ops, uint32_t n_ops);
+hb_status group_stats(hb_ctx* g, hb_stats_t* out);
+}  // namespace
+
 // ================================================================ C ABI
 extern "C" {
 
@@ -548,6 +558,7 @@ hb_status hb_ctx_create(int32_t device, hb_ctx** out) {
 
 hb_status hb_ctx_destroy(hb_ctx* c) {
     if (!c) return HB_ERR_ARG;
+    if (c->is_group()) return group_destroy(c);
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     for (DevBuf* b : {&c->bsk_f, &c->ksk, &c->ksk_planes, &c->ks_dig, &c->wtab, &c->scratch_a, &c->scratch_b, &c->atil, &c->lin_stage, &c->jobs_dev, &c->stage_dev, &c->idx_dev}) b->release();
@@ -557,6 +568,7 @@ hb_status hb_ctx_destroy(hb_ctx* c) {
         for (auto& t : s.t) cudaEventDestroy(t);
     }
     for (auto& ev : c->ev) cudaEventDestroy(ev);
+    if (c->level_ev) cudaEventDestroy(c->level_ev);
     cudaStreamDestroy(c->stream);
     delete c;
     return HB_OK;
@@ -564,6 +576,11 @@ hb_status hb_ctx_destroy(hb_ctx* c) {
 
 hb_status hb_set_params(hb_ctx* c, const hb_params* p) {
     if (!c || !p) return HB_ERR_ARG;
+    if (c->is_group()) {
+        for (hb_ctx* m : c->subs) if (hb_status s = lift(c, m, hb_set_params(m, p))) return s;
+        c->p = *p; c->have_params = true; c->have_bsk = c->have_ksk = false;
+        return HB_OK;
+    }
     if (p->torus_bits != 32 && p->torus_bits != 64) return fail(c, HB_ERR_ARG, "torus_bits must be 32 or 64");
     const int sh = find_shape(*p);
     if (sh < 0) return fail(c, HB_ERR_UNSUPPORTED, "no sm_100a kernel instance for this (torus_bits, N, k, pbs_level)");
@@ -585,6 +602,7 @@ hb_status hb_set_params(hb_ctx* c, const hb_params* p) {
 
 hb_status hb_load_bsk(hb_ctx* c, const void* bsk, size_t bytes) {
     if (!c || !bsk) return HB_ERR_ARG;
+    if (c->is_group()) { if (hb_status s = group_each(c, &hb_load_bsk, bsk, bytes)) return s; c->have_bsk = true; return HB_OK; }
     if (!c->have_params) return fail(c, HB_ERR_STATE, "hb_set_params not called");
     CU(c, cudaSetDevice(c->device));
     const hb_params& p = c->p;
@@ -609,6 +627,7 @@ hb_status hb_load_bsk(hb_ctx* c, const void* bsk, size_t bytes) {
 
 hb_status hb_load_ksk(hb_ctx* c, const void* ksk, size_t bytes) {
     if (!c || !ksk) return HB_ERR_ARG;
+    if (c->is_group()) { if (hb_status s = group_each(c, &hb_load_ksk, ksk, bytes)) return s; c->have_ksk = true; return HB_OK; }
     if (!c->have_params) return fail(c, HB_ERR_STATE, "hb_set_params not called");
     CU(c, cudaSetDevice(c->device));
     const hb_params& p = c->p;
@@ -631,11 +650,12 @@ hb_status hb_load_ksk(hb_ctx* c, const void* ksk, size_t bytes) {
 
 uint32_t hb_ct_words(const hb_ctx* c) { return c && c->have_params ? ct_words(c) : 0; }
 uint32_t hb_wire_stride(const hb_ctx* c) { return c && c->have_params ? pad4(ct_words(c)) : 0; }
-void* hb_stream(hb_ctx* c) { return c ? (void*)c->stream : nullptr; }
+void* hb_stream(hb_ctx* c) { return !c ? nullptr : c->is_group() ? (void*)c->subs[0]->stream : (void*)c->stream; }
 
 hb_status hb_wires_create(hb_ctx* c, uint32_t n_wires, hb_wires** out) {
     if (!c || !out || !n_wires) return HB_ERR_ARG;
     if (!c->have_params) return fail(c, HB_ERR_STATE, "hb_set_params not called");
+    if (c->is_group()) return group_wires_create(c, n_wires, out);
     CU(c, cudaSetDevice(c->device));
     hb_wires* w = new hb_wires();
     w->ctx = c; w->n_wires = n_wires; w->owned = true;
@@ -648,6 +668,7 @@ hb_status hb_wires_create(hb_ctx* c, uint32_t n_wires, hb_wires** out) {
 }
 hb_status hb_wires_attach(hb_ctx* c, void* dev, uint32_t n_wires, hb_wires** out) {
     if (!c || !out || !dev || !n_wires) return HB_ERR_ARG;
+    if (c->is_group()) return fail(c, HB_ERR_UNSUPPORTED, "hb_wires_attach: a multi-device context owns its wire replicas");
     if (!c->have_params) return fail(c, HB_ERR_STATE, "hb_set_params not called");
     hb_wires* w = new hb_wires();
     w->ctx = c; w->n_wires = n_wires; w->owned = false; w->dev = dev;
@@ -656,11 +677,13 @@ hb_status hb_wires_attach(hb_ctx* c, void* dev, uint32_t n_wires, hb_wires** out
 }
 hb_status hb_wires_destroy(hb_wires* w) {
     if (!w) return HB_ERR_ARG;
+    for (hb_wires* m : w->subs) hb_wires_destroy(m);
+    if (!w->subs.empty()) { delete w; return HB_OK; }
     if (w->owned && w->dev) { cudaSetDevice(w->ctx->device); cudaStreamSynchronize(w->ctx->stream); cudaFree(w->dev); }
     delete w;
     return HB_OK;
 }
-void* hb_wires_device_ptr(hb_wires* w) { return w ? w->dev : nullptr; }
+void* hb_wires_device_ptr(hb_wires* w) { return !w ? nullptr : w->subs.empty() ? w->dev : w->subs[0]->dev; }
 
 static hb_status check_idx(hb_wires* w, const uint32_t* idx, uint32_t cnt) {
     if (idx) { for (uint32_t i = 0; i < cnt; ++i) if (idx[i] >= w->n_wires) return fail(w->ctx, HB_ERR_ARG, "wire index out of range"); }
@@ -671,6 +694,10 @@ static hb_status check_idx(hb_wires* w, const uint32_t* idx, uint32_t cnt) {
 hb_status hb_wires_write(hb_wires* w, const uint32_t* idx, uint32_t cnt, const void* host) {
     if (!w || (!host && cnt)) return HB_ERR_ARG;
     if (!cnt) return HB_OK;
+    if (!w->subs.empty()) {                                   // every replica
+        for (hb_wires* m : w->subs) if (hb_status s = lift(w->ctx, m->ctx, hb_wires_write(m, idx, cnt, host))) return s;
+        return HB_OK;
+    }
     hb_ctx* c = w->ctx;
     if (hb_status s = check_idx(w, idx, cnt)) return s;
     CU(c, cudaSetDevice(c->device));
@@ -696,6 +723,10 @@ hb_status hb_wires_write(hb_wires* w, const uint32_t* idx, uint32_t cnt, const v
 hb_status hb_wires_read(hb_wires* w, const uint32_t* idx, uint32_t cnt, void* host) {
     if (!w || (!host && cnt)) return HB_ERR_ARG;
     if (!cnt) return HB_OK;
+    if (!w->subs.empty()) {                                   // replicas are coherent between levels: read the first
+        if (hb_status s = hb_sync(w->ctx)) return s;
+        return lift(w->ctx, w->subs[0]->ctx, hb_wires_read(w->subs[0], idx, cnt, host));
+    }
     hb_ctx* c = w->ctx;
     if (hb_status s = check_idx(w, idx, cnt)) return s;
     CU(c, cudaSetDevice(c->device));
@@ -722,6 +753,18 @@ static constexpr size_t BIG_COPY = 4u << 20;   // row-range copies from this siz
 hb_status hb_wires_write_rows(hb_wires* w, uint32_t first, uint32_t cnt, const void* host) {
     if (!w || (!host && cnt)) return HB_ERR_ARG;
     if (!cnt) return HB_OK;
+    if (!w->subs.empty()) {
+        // one PCIe copy into the first replica, then device-to-device copies over NVLink (not n_devices host copies)
+        hb_wires* w0 = w->subs[0];
+        if (hb_status s = lift(w->ctx, w0->ctx, hb_wires_write_rows(w0, first, cnt, host))) return s;
+        const size_t ts = tsize(w0->ctx), stride = hb_wire_stride(w0->ctx), off = (size_t)first * stride * ts, len = (size_t)cnt * stride * ts;
+        for (size_t d = 1; d < w->subs.size(); ++d) {
+            hb_wires* m = w->subs[d];
+            CU(w->ctx, cudaSetDevice(m->ctx->device));
+            CU(w->ctx, cudaMemcpyPeerAsync((char*)m->dev + off, m->ctx->device, (const char*)w0->dev + off, w0->ctx->device, len, m->ctx->stream));
+        }
+        return hb_sync(w->ctx);
+    }
     hb_ctx* c = w->ctx;
     if ((uint64_t)first + cnt > w->n_wires) return fail(c, HB_ERR_ARG, "wire row range out of bounds");
     CU(c, cudaSetDevice(c->device));
@@ -744,6 +787,10 @@ hb_status hb_wires_write_rows(hb_wires* w, uint32_t first, uint32_t cnt, const v
 hb_status hb_wires_read_rows(hb_wires* w, uint32_t first, uint32_t cnt, void* host) {
     if (!w || (!host && cnt)) return HB_ERR_ARG;
     if (!cnt) return HB_OK;
+    if (!w->subs.empty()) {
+        if (hb_status s = hb_sync(w->ctx)) return s;
+        return lift(w->ctx, w->subs[0]->ctx, hb_wires_read_rows(w->subs[0], first, cnt, host));
+    }
     hb_ctx* c = w->ctx;
     if ((uint64_t)first + cnt > w->n_wires) return fail(c, HB_ERR_ARG, "wire row range out of bounds");
     CU(c, cudaSetDevice(c->device));
@@ -766,6 +813,10 @@ hb_status hb_wires_read_rows(hb_wires* w, uint32_t first, uint32_t cnt, void* ho
 
 hb_status hb_wires_set_trivial(hb_wires* w, const uint32_t* idx, uint32_t cnt, const uint64_t* pt) {
     if (!w || !idx || !pt) return HB_ERR_ARG;
+    if (!w->subs.empty()) {
+        for (hb_wires* m : w->subs) if (hb_status s = lift(w->ctx, m->ctx, hb_wires_set_trivial(m, idx, cnt, pt))) return s;
+        return hb_sync(w->ctx);                               // a replica must not receive a peer's pushes before its own initialisation ran
+    }
     hb_ctx* c = w->ctx;
     if (hb_status s = check_idx(w, idx, cnt)) return s;
     CU(c, cudaSetDevice(c->device));
@@ -780,6 +831,11 @@ hb_status hb_wires_set_trivial(hb_wires* w, const uint32_t* idx, uint32_t cnt, c
 
 hb_status hb_sync(hb_ctx* c) {
     if (!c) return HB_ERR_ARG;
+    if (c->is_group()) {
+        for (hb_ctx* m : c->subs) if (hb_status s = lift(c, m, hb_sync(m))) return s;
+        return HB_OK;
+    }
+    CU(c, cudaSetDevice(c->device));
     CU(c, cudaStreamSynchronize(c->stream));
     return HB_OK;
 }
@@ -797,6 +853,8 @@ hb_status hb_debug_phase_clocks(hb_ctx* c, double* out8) {
 
 hb_status hb_stats(hb_ctx* c, hb_stats_t* out) {
     if (!c || !out) return HB_ERR_ARG;
+    if (c->is_group()) return group_stats(c, out);
+    CU(c, cudaSetDevice(c->device));
     CtxExtra* ex = extra_of(c);
     // drain in submission order so pbs_ms / ks_ms end up describing the latest level
     for (uint64_t q = 0; q < NSLOT; ++q) {
@@ -805,6 +863,7 @@ hb_status hb_stats(hb_ctx* c, hb_stats_t* out) {
         CU(c, cudaEventSynchronize(s.done));
         fold_timing(c, s, q + 1 < NSLOT ? &ex->slots[(ex->next + q + 1) % NSLOT] : nullptr);
     }
+    c->stats.n_devices = 1;
     *out = c->stats;
     return HB_OK;
 }
@@ -841,6 +900,7 @@ inline uint64_t bool_as_lut(int op) {
 extern "C" {
 
 hb_status hb_eval_level(hb_ctx* c, hb_wires* w, const hb_gate* gates, uint32_t n_gates) {
+    if (c && c->is_group()) return group_eval_level(c, w, gates, n_gates);
     if (hb_status s = check_ready(c)) return s;
     if (!w || w->ctx != c || (!gates && n_gates)) return fail(c, HB_ERR_ARG, "hb_eval_level: bad arguments");
     if (!n_gates) return HB_OK;
@@ -944,12 +1004,18 @@ hb_status hb_eval_level(hb_ctx* c, hb_wires* w, const hb_gate* gates, uint32_t n
     CU(c, cudaEventRecord(slot->t[2], c->stream));
     slot->first_is_pbs = p.order == 0; slot->pending = true;
     if (hb_status s = launch_lin(c, w->dev, wstride, dl, (uint32_t)lj.size(), ct_words(c), lin_hazard(lj))) return s;
+    if (w->peers.n_dst) {                                      // member of a multi-device group: exchange this share's output rows
+        if (p.order == 0) { if (hb_status s = launch_push(c, w, dk, (uint32_t)kj.size())) return s; }
+        else if (hb_status s = launch_push(c, w, dp, (uint32_t)pj.size())) return s;
+        if (hb_status s = launch_push(c, w, dl, (uint32_t)lj.size())) return s;
+    }
     CU(c, cudaEventRecord(slot->done, c->stream));
     c->stats.levels++;
     return HB_OK;
 }
 
 hb_status hb_eval_shortint_ops(hb_ctx* c, hb_wires* w, const hb_sop* ops, uint32_t n_ops) {
+    if (c && c->is_group()) return group_eval_sops(c, w, ops, n_ops);
     if (hb_status s = check_ready(c)) return s;
     if (!w || w->ctx != c || (!ops && n_ops)) return fail(c, HB_ERR_ARG, "hb_eval_shortint_ops: bad arguments");
     if (c->p.order != 1) return fail(c, HB_ERR_UNSUPPORTED, "hb_eval_shortint_ops needs a shortint (order 1) parameter set");
@@ -989,11 +1055,13 @@ hb_status hb_eval_shortint_ops(hb_ctx* c, hb_wires* w, const hb_sop* ops, uint32
         if (hb_status s = launch_pbs(c, c->scratch_b.p, sstride, w->dev, wstride, dp, (uint32_t)pj.size())) return s;
         CU(c, cudaEventRecord(slot->t[2], c->stream));
         slot->first_is_pbs = 0; slot->pending = true;
+        if (hb_status s = launch_push(c, w, dp, (uint32_t)pj.size())) return s;
         CU(c, cudaEventRecord(slot->done, c->stream));
     }
     if (!lin.empty()) {
         if (hb_status s = upload_jobs(c, {}, lin, {}, &dp, &dk, &dl, &slot)) return s;
         if (hb_status s = launch_lincomb(c, w->dev, wstride, dk, (uint32_t)lin.size(), ct_words(c), lincomb_hazard(lin))) return s;
+        if (hb_status s = launch_push(c, w, dk, (uint32_t)lin.size())) return s;
         CU(c, cudaEventRecord(slot->done, c->stream));
     }
     c->stats.levels++;
@@ -1001,6 +1069,7 @@ hb_status hb_eval_shortint_ops(hb_ctx* c, hb_wires* w, const hb_sop* ops, uint32
 }
 
 hb_status hb_pbs_batch(hb_ctx* c, const void* lwe_in, const void* tv, int32_t shared_tv, uint32_t count, void* lwe_out) {
+    if (c && c->is_group()) return lift(c, c->subs[0], hb_pbs_batch(c->subs[0], lwe_in, tv, shared_tv, count, lwe_out));
     if (hb_status s = check_ready(c)) return s;
     if (!lwe_in || !tv || !lwe_out) return fail(c, HB_ERR_ARG, "hb_pbs_batch: null buffer");
     if (!count) return HB_OK;
@@ -1034,6 +1103,7 @@ hb_status hb_pbs_batch(hb_ctx* c, const void* lwe_in, const void* tv, int32_t sh
 }
 
 hb_status hb_keyswitch_batch(hb_ctx* c, const void* lwe_in, uint32_t count, void* lwe_out) {
+    if (c && c->is_group()) return lift(c, c->subs[0], hb_keyswitch_batch(c->subs[0], lwe_in, count, lwe_out));
     if (hb_status s = check_ready(c)) return s;
     if (!lwe_in || !lwe_out) return fail(c, HB_ERR_ARG, "hb_keyswitch_batch: null buffer");
     if (!count) return HB_OK;
@@ -1056,6 +1126,7 @@ hb_status hb_keyswitch_batch(hb_ctx* c, const void* lwe_in, uint32_t count, void
 
 hb_status hb_measure_fp64_peak(hb_ctx* c, double* tflops) {
     if (!c || !tflops) return HB_ERR_ARG;
+    if (c->is_group()) return lift(c, c->subs[0], hb_measure_fp64_peak(c->subs[0], tflops));
     CU(c, cudaSetDevice(c->device));
     const int blocks = c->sm_count * 4, threads = 512, iters = 1 << 15;
     CU(c, c->stage_dev.ensure((size_t)blocks * threads * sizeof(double)));
@@ -1076,3 +1147,132 @@ hb_status hb_measure_fp64_peak(hb_ctx* c, double* tflops) {
 }
 
 }  // extern "C"
+
+// ================================================================ multi-device group
+// One host thread drives every device: all launches are asynchronous, so the per-device shares of a level run concurrently.
+namespace {
+
+hb_status group_destroy(hb_ctx* g) {
+    for (hb_ctx* m : g->subs) hb_ctx_destroy(m);
+    delete g;
+    return HB_OK;
+}
+
+hb_status group_each(hb_ctx* g, hb_status (*f)(hb_ctx*, const void*, size_t), const void* a, size_t b) {
+    for (hb_ctx* m : g->subs) if (hb_status s = lift(g, m, f(m, a, b))) return s;
+    return HB_OK;
+}
+
+hb_status group_wires_create(hb_ctx* g, uint32_t n_wires, hb_wires** out) {
+    hb_wires* w = new hb_wires();
+    w->ctx = g; w->n_wires = n_wires;
+    for (hb_ctx* m : g->subs) {
+        hb_wires* r = nullptr;
+        if (hb_status s = lift(g, m, hb_wires_create(m, n_wires, &r))) { hb_wires_destroy(w); return s; }
+        w->subs.push_back(r);
+    }
+    for (size_t d = 0; d < w->subs.size(); ++d) {
+        PushArgs& P = w->subs[d]->peers;
+        P.n_dst = 0;
+        for (size_t e = 0; e < w->subs.size(); ++e) if (e != d) P.dst[P.n_dst++] = w->subs[e]->dev;
+    }
+    if (hb_status s = hb_sync(g)) { hb_wires_destroy(w); return s; }      // every replica zeroed before any peer may push into it
+    *out = w;
+    return HB_OK;
+}
+
+// how many devices share a batch of `n` items: a slice narrower than shard_min cannot make the batch faster
+uint32_t group_width(const hb_ctx* g, uint32_t n) {
+    const uint32_t D = (uint32_t)g->subs.size(), per = g->shard_min ? g->shard_min : 1;
+    uint32_t d = (n + per - 1) / per;
+    return d < 1 ? 1 : d > D ? D : d;
+}
+
+// after every member enqueued its share (+ pushes): per-device "share done" events, and every stream waits for all of them,
+// so no device starts the next level before all replicas hold this level's outputs
+hb_status group_level_barrier(hb_ctx* g, uint32_t active) {
+    for (uint32_t d = 0; d < active; ++d) {
+        hb_ctx* m = g->subs[d];
+        CU(g, cudaSetDevice(m->device));
+        CU(g, cudaEventRecord(m->level_ev, m->stream));
+    }
+    for (hb_ctx* m : g->subs) {
+        CU(g, cudaSetDevice(m->device));
+        for (uint32_t e = 0; e < active; ++e)
+            if (g->subs[e] != m) CU(g, cudaStreamWaitEvent(m->stream, g->subs[e]->level_ev, 0));
+    }
+    return HB_OK;
+}
+
+template <class Item, class F> hb_status group_run(hb_ctx* g, hb_wires* w, const Item* items, uint32_t n, F eval) {
+    if (hb_status s = check_ready(g)) return s;
+    if (!w || w->ctx != g || w->subs.size() != g->subs.size() || (!items && n)) return fail(g, HB_ERR_ARG, "multi-device batch: bad arguments");
+    if (!n) return HB_OK;
+    const uint32_t active = group_width(g, n), per = (n + active - 1) / active;
+    for (uint32_t d = 0; d < active; ++d) {
+        const uint32_t lo = d * per, hi = lo + per < n ? lo + per : n;
+        if (lo >= hi) continue;
+        if (hb_status s = lift(g, g->subs[d], eval(g->subs[d], w->subs[d], items + lo, hi - lo))) return s;
+    }
+    g->stats.levels++;
+    if (active > 1) g->stats.sharded_levels++;
+    return group_level_barrier(g, active);
+}
+
+hb_status group_eval_level(hb_ctx* g, hb_wires* w, const hb_gate* gates, uint32_t n_gates) {
+    return group_run(g, w, gates, n_gates, [](hb_ctx* m, hb_wires* r, const hb_gate* p, uint32_t c) { return hb_eval_level(m, r, p, c); });
+}
+hb_status group_eval_sops(hb_ctx* g, hb_wires* w, const hb_sop* ops, uint32_t n_ops) {
+    if (g->p.order != 1) return fail(g, HB_ERR_UNSUPPORTED, "hb_eval_shortint_ops needs a shortint (order 1) parameter set");
+    return group_run(g, w, ops, n_ops, [](hb_ctx* m, hb_wires* r, const hb_sop* p, uint32_t c) { return hb_eval_shortint_ops(m, r, p, c); });
+}
+
+hb_status group_stats(hb_ctx* g, hb_stats_t* out) {
+    hb_stats_t t{};
+    for (hb_ctx* m : g->subs) {
+        hb_stats_t s{};
+        if (hb_status e = lift(g, m, hb_stats(m, &s))) return e;
+        t.pbs_count += s.pbs_count; t.ks_count += s.ks_count; t.kernel_launches += s.kernel_launches; t.push_bytes += s.push_bytes;
+        t.pbs_ms = s.pbs_ms > t.pbs_ms ? s.pbs_ms : t.pbs_ms; t.ks_ms = s.ks_ms > t.ks_ms ? s.ks_ms : t.ks_ms;
+        t.pbs_ms_total = s.pbs_ms_total > t.pbs_ms_total ? s.pbs_ms_total : t.pbs_ms_total;
+        t.ks_ms_total = s.ks_ms_total > t.ks_ms_total ? s.ks_ms_total : t.ks_ms_total;
+        t.gap_ms_total = s.gap_ms_total > t.gap_ms_total ? s.gap_ms_total : t.gap_ms_total;
+    }
+    t.levels = g->stats.levels; t.sharded_levels = g->stats.sharded_levels; t.n_devices = (uint32_t)g->subs.size();
+    *out = t;
+    return HB_OK;
+}
+
+}  // namespace
+
+extern "C" hb_status hb_ctx_create_multi(const int32_t* devices, int32_t n_devices, uint32_t min_gates_per_device, hb_ctx** out) {
+    if (!out || !devices || n_devices < 1 || n_devices > HB_MAX_DEV) return fail(nullptr, HB_ERR_ARG, "hb_ctx_create_multi: 1..8 devices");
+    *out = nullptr;
+    for (int a = 0; a < n_devices; ++a)
+        for (int b = a + 1; b < n_devices; ++b)
+            if (devices[a] == devices[b]) return fail(nullptr, HB_ERR_ARG, "hb_ctx_create_multi: devices must be distinct");
+    hb_ctx* g = new hb_ctx();
+    for (int a = 0; a < n_devices; ++a) {
+        hb_ctx* m = nullptr;
+        if (hb_status s = hb_ctx_create(devices[a], &m)) { group_destroy(g); return s; }
+        g->subs.push_back(m);
+        if (cudaEventCreateWithFlags(&m->level_ev, cudaEventDisableTiming) != cudaSuccess) { group_destroy(g); return fail(nullptr, HB_ERR_CUDA, "cudaEventCreate"); }
+    }
+    // every pair must be peer-mapped: the level exchange is device-initiated stores into the peers' replicas
+    for (int a = 0; a < n_devices; ++a)
+        for (int b = 0; b < n_devices; ++b) {
+            if (a == b) continue;
+            int can = 0;
+            cudaDeviceCanAccessPeer(&can, devices[a], devices[b]);
+            if (!can) { group_destroy(g); return fail(nullptr, HB_ERR_UNSUPPORTED, "hb_ctx_create_multi: devices are not peer-accessible"); }
+            cudaSetDevice(devices[a]);
+            const cudaError_t e = cudaDeviceEnablePeerAccess(devices[b], 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { group_destroy(g); return fail(nullptr, HB_ERR_CUDA, std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e)); }
+            (void)cudaGetLastError();
+        }
+    g->device = devices[0];
+    g->sm_count = g->subs[0]->sm_count;
+    g->shard_min = min_gates_per_device ? min_gates_per_device : (uint32_t)g->sm_count;
+    *out = g;
+    return HB_OK;
+}

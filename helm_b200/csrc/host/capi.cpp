@@ -149,21 +149,27 @@ int hh_read_input_csv(const char* path, const char* ptxt_type, char* buf, size_t
 // ---------------------------------------------------------------- encrypted sessions
 extern "C" {
 
-int hh_session_create(const char* param_set, int device, uint64_t seed, const uint8_t* lwe_sk, const uint8_t* glwe_sk,
-                      const void* bsk, size_t bsk_bytes, const void* ksk, size_t ksk_bytes, hh_session** out) {
+int hh_session_create_multi(const char* param_set, const int* devices, int n_devices, uint64_t seed, const uint8_t* lwe_sk,
+                            const uint8_t* glwe_sk, const void* bsk, size_t bsk_bytes, const void* ksk, size_t ksk_bytes, hh_session** out) {
     return guarded([&] {
+        if (!devices || n_devices < 1) throw Error("hh_session_create_multi: no devices");
+        const std::vector<int> dv(devices, devices + n_devices);
         auto s = std::make_unique<hh_session>();
         s->p = params_by_name(param_set);
         if (lwe_sk && glwe_sk && bsk && ksk) {
             s->ck = ClientKey::from_raw(s->p, lwe_sk, glwe_sk, seed);
-            s->sk = std::make_unique<ServerKey>(s->p, bsk, bsk_bytes, ksk, ksk_bytes, device);
+            s->sk = std::make_unique<ServerKey>(s->p, bsk, bsk_bytes, ksk, ksk_bytes, dv);
         } else {
             ServerKeyMaterial m;
             gen_keys(s->p, seed, &s->ck, &m);
-            s->sk = std::make_unique<ServerKey>(s->p, m, device);
+            s->sk = std::make_unique<ServerKey>(s->p, m.bsk.data(), m.bsk.size(), m.ksk.data(), m.ksk.size(), dv);
         }
         *out = s.release();
     });
+}
+int hh_session_create(const char* param_set, int device, uint64_t seed, const uint8_t* lwe_sk, const uint8_t* glwe_sk,
+                      const void* bsk, size_t bsk_bytes, const void* ksk, size_t ksk_bytes, hh_session** out) {
+    return hh_session_create_multi(param_set, &device, 1, seed, lwe_sk, glwe_sk, bsk, bsk_bytes, ksk, ksk_bytes, out);
 }
 void hh_session_free(hh_session* s) { delete s; }
 
@@ -247,6 +253,12 @@ int hh_session_stats(hh_session* s, uint64_t* out4) {
     return guarded([&] {
         const hb_stats_t st = s->sk->stats();
         out4[0] = st.pbs_count; out4[1] = st.ks_count; out4[2] = st.levels; out4[3] = st.kernel_launches;
+    });
+}
+int hh_session_stats_multi(hh_session* s, uint64_t* out3) {
+    return guarded([&] {
+        const hb_stats_t st = s->sk->stats();
+        out3[0] = st.n_devices; out3[1] = st.sharded_levels; out3[2] = st.push_bytes;
     });
 }
 

@@ -11,8 +11,10 @@ static void ck_status(hb_ctx* c, hb_status s, const char* what) {
 }
 
 // ---------------------------------------------------------------- ServerKey
-void ServerKey::init(const void* bsk, size_t bsk_bytes, const void* ksk, size_t ksk_bytes, int device) {
-    hb_status s = hb_ctx_create(device, &ctx_);
+void ServerKey::init(const void* bsk, size_t bsk_bytes, const void* ksk, size_t ksk_bytes, const std::vector<int>& devices) {
+    if (devices.empty()) throw Error("ServerKey: no device");
+    std::vector<int32_t> dv(devices.begin(), devices.end());
+    hb_status s = dv.size() == 1 ? hb_ctx_create(dv[0], &ctx_) : hb_ctx_create_multi(dv.data(), (int32_t)dv.size(), 0, &ctx_);
     if (s != HB_OK) throw Error(std::string("hb_ctx_create failed: ") + hb_last_error(nullptr));
     try {
         ck_status(ctx_, hb_set_params(ctx_, &p_.hb), "hb_set_params");
@@ -21,10 +23,13 @@ void ServerKey::init(const void* bsk, size_t bsk_bytes, const void* ksk, size_t 
     } catch (...) { hb_ctx_destroy(ctx_); ctx_ = nullptr; throw; }
 }
 ServerKey::ServerKey(const Params& p, const ServerKeyMaterial& k, int device) : p_(p) {
-    init(k.bsk.data(), k.bsk.size(), k.ksk.data(), k.ksk.size(), device);
+    init(k.bsk.data(), k.bsk.size(), k.ksk.data(), k.ksk.size(), {device});
 }
 ServerKey::ServerKey(const Params& p, const void* bsk, size_t bb, const void* ksk, size_t kb, int device) : p_(p) {
-    init(bsk, bb, ksk, kb, device);
+    init(bsk, bb, ksk, kb, {device});
+}
+ServerKey::ServerKey(const Params& p, const void* bsk, size_t bb, const void* ksk, size_t kb, const std::vector<int>& devices) : p_(p) {
+    init(bsk, bb, ksk, kb, devices);
 }
 ServerKey::~ServerKey() { if (ctx_) hb_ctx_destroy(ctx_); }
 hb_stats_t ServerKey::stats() const { hb_stats_t st{}; ck_status(ctx_, hb_stats(ctx_, &st), "hb_stats"); return st; }

@@ -16,13 +16,15 @@ class ServerKey {
 public:
     ServerKey(const Params& p, const ServerKeyMaterial& keys, int device = 0);
     ServerKey(const Params& p, const void* bsk, size_t bsk_bytes, const void* ksk, size_t ksk_bytes, int device = 0);
+    // one server key over several GPUs of the node (hb_ctx_create_multi): keys replicated, wide levels sharded inside the engine
+    ServerKey(const Params& p, const void* bsk, size_t bsk_bytes, const void* ksk, size_t ksk_bytes, const std::vector<int>& devices);
     ~ServerKey();
     ServerKey(const ServerKey&) = delete;
     hb_ctx* ctx() const { return ctx_; }
     const Params& params() const { return p_; }
     hb_stats_t stats() const;
 private:
-    void init(const void* bsk, size_t bsk_bytes, const void* ksk, size_t ksk_bytes, int device);
+    void init(const void* bsk, size_t bsk_bytes, const void* ksk, size_t ksk_bytes, const std::vector<int>& devices);
     Params p_;
     hb_ctx* ctx_ = nullptr;
 };

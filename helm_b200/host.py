@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libhelm_host.so")
 EXPORTS = ["hh_last_error", "hh_circuit_load", "hh_circuit_load_text", "hh_circuit_free", "hh_circuit_count",
            "hh_circuit_level_width", "hh_circuit_names", "hh_circuit_describe", "hh_circuit_eval_plain", "hh_read_input_csv", "hh_chacha20_block", "hh_preprocess_yosys", "hh_preprocess_yosys_mode", "hh_preprocess_assign_dict",
-           "hh_session_create", "hh_session_free", "hh_session_run", "hh_session_run_arith", "hh_session_stats"]
+           "hh_session_create", "hh_session_create_multi", "hh_session_free", "hh_session_run", "hh_session_run_arith", "hh_session_stats", "hh_session_stats_multi"]
 _LIB = None
 
 
@@ -44,6 +44,8 @@ def lib():
         L.hh_chacha20_block.argtypes = [vp, vp, vp]
         L.hh_chacha20_block.restype = None
         L.hh_session_create.argtypes = [cp, C.c_int, C.c_uint64, vp, vp, vp, sz, vp, sz, C.POINTER(vp)]
+        L.hh_session_create_multi.argtypes = [cp, C.POINTER(C.c_int), C.c_int, C.c_uint64, vp, vp, vp, sz, vp, sz, C.POINTER(vp)]
+        L.hh_session_stats_multi.argtypes = [vp, C.POINTER(C.c_uint64)]
         L.hh_session_free.argtypes = [vp]
         L.hh_session_run.argtypes = [vp, vp, cp, C.c_int, C.c_int, C.c_int, vp, sz, C.POINTER(sz), C.POINTER(C.c_double)]
         L.hh_session_run_arith.argtypes = [vp, vp, cp, cp, C.c_int, C.c_int, C.c_int, vp, sz, C.POINTER(sz),
@@ -159,16 +161,19 @@ class Circuit:
 class Session:
     """Keys + engine context (reference: gen_keys + GateCircuit/LutCircuit::new)."""
 
-    def __init__(self, param_set, device=0, seed=1, raw_keys=None):
+    def __init__(self, param_set, device=0, seed=1, raw_keys=None, devices=None):
+        """devices=[0, 1, ...]: one session over several GPUs of the node (levels sharded inside the engine)."""
         self.L = lib()
         self.h = C.c_void_p()
+        dv = list(devices) if devices is not None else [device]
+        arr = (C.c_int * len(dv))(*dv)
         if raw_keys is None:
-            _ck(self.L.hh_session_create(param_set.encode(), device, seed, None, None, None, 0, None, 0, C.byref(self.h)))
+            _ck(self.L.hh_session_create_multi(param_set.encode(), arr, len(dv), seed, None, None, None, 0, None, 0, C.byref(self.h)))
         else:
             lwe_sk, glwe_sk, bsk, ksk = raw_keys       # numpy arrays (uint8, uint8, torus, torus)
             self._keep = raw_keys
-            _ck(self.L.hh_session_create(param_set.encode(), device, seed, lwe_sk.ctypes.data, glwe_sk.ctypes.data,
-                                         bsk.ctypes.data, bsk.nbytes, ksk.ctypes.data, ksk.nbytes, C.byref(self.h)))
+            _ck(self.L.hh_session_create_multi(param_set.encode(), arr, len(dv), seed, lwe_sk.ctypes.data, glwe_sk.ctypes.data,
+                                               bsk.ctypes.data, bsk.nbytes, ksk.ctypes.data, ksk.nbytes, C.byref(self.h)))
 
     def close(self):
         if self.h:
@@ -199,4 +204,8 @@ class Session:
     def stats(self):
         out = (C.c_uint64 * 4)()
         _ck(self.L.hh_session_stats(self.h, out))
-        return dict(zip(("pbs_count", "ks_count", "levels", "kernel_launches"), (int(v) for v in out)))
+        d = dict(zip(("pbs_count", "ks_count", "levels", "kernel_launches"), (int(v) for v in out)))
+        m = (C.c_uint64 * 3)()
+        _ck(self.L.hh_session_stats_multi(self.h, m))
+        d.update(zip(("n_devices", "sharded_levels", "push_bytes"), (int(v) for v in m)))
+        return d

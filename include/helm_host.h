@@ -61,6 +61,11 @@ void hh_chacha20_block(const uint32_t* key8, const uint32_t* w12_15, uint32_t* o
 int hh_session_create(const char* param_set, int device, uint64_t seed,
                       const uint8_t* lwe_sk, const uint8_t* glwe_sk, const void* bsk, size_t bsk_bytes,
                       const void* ksk, size_t ksk_bytes, hh_session** out);
+/* the same over several GPUs of this node (engine: hb_ctx_create_multi): keys and wires replicated per device, levels wider than
+ * one gate per SM split across the devices inside hb_eval_level, outputs exchanged over NVLink -- the circuit surface is unchanged */
+int hh_session_create_multi(const char* param_set, const int* devices, int n_devices, uint64_t seed,
+                            const uint8_t* lwe_sk, const uint8_t* glwe_sk, const void* bsk, size_t bsk_bytes,
+                            const void* ksk, size_t ksk_bytes, hh_session** out);
 void hh_session_free(hh_session*);
 /* encrypt_inputs -> cycles x (evaluate_encrypted [+ evaluate_ready]) -> decrypt_outputs.  Output wires as
  * "wire=value\n"; if all_wires != 0 every wire that carries a value is decrypted (the reference's tests compare every
@@ -74,6 +79,8 @@ int hh_session_run_arith(hh_session*, const hh_circuit*, const char* inputs, con
                          uint64_t* counts);
 /* engine statistics of the session: pbs_count, ks_count, levels, kernel_launches */
 int hh_session_stats(hh_session*, uint64_t* out4);
+/* multi-device statistics: n_devices, levels / batches split over more than one device, bytes pushed into peer replicas */
+int hh_session_stats_multi(hh_session*, uint64_t* out3);
 
 #ifdef __cplusplus
 }
