@@ -54,3 +54,11 @@ def test_product_never_imports_oracle():
                 txt = open(os.path.join(dp, f), errors="ignore").read()
                 assert "tfhe_oracle" not in txt and "liboracle" not in txt and "from oracle" not in txt \
                     and "import oracle" not in txt, "%s references the oracle" % f
+
+
+def test_integration_doc_declares_every_export():
+    """INTEGRATION.md's Rust shim must bind every export of the header (15 of 25 were declared)."""
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    rust = set(re.findall(r"pub fn (hb_[a-z0-9_]+)\(", doc))
+    assert rust == set(declared_symbols())
+    assert "pub struct HbSop" in doc and "pub struct HbStats" in doc
