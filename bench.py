@@ -290,6 +290,63 @@ def iscas_cpu_latency(name):
             "cpu_outputs_verified": bool(ok)}
 
 
+def f_cmux(k, l, N):
+    """algorithmic flops of one CMUX step: ((k+1)l + (k+1)) transforms of M = N/2 points + (k+1)^2 l M complex MACs"""
+    M = N // 2
+    return ((k + 1) * l + (k + 1)) * (5 * M * np.log2(M) + 6 * M) + (k + 1) ** 2 * l * M * 8
+
+
+def shortint_leg(name, device, fp64_peak, W=16384, steps=3, warmup=2):
+    """LUT-mode throughput (the path of lut(), /root/reference/src/gates.rs:754-785, keygen /root/reference/src/bin/helm.rs:301):
+    W two-input LUT gates per level on a u64 parameter set, keyswitch -> PBS each, wires resident; PBS kernel time from the
+    engine's event ring; fraction of the FP64 peak with the set's own F_pbs (M1C1 86.9 MFLOP, M2C2 194.5 MFLOP)."""
+    import helm_b200
+    from helm_b200 import engine as E
+    from oracle import oracle as O
+    K = O.Keys(name, seed=3)
+    eng = helm_b200.Engine(K.params, device=device)
+    eng.load_keys(K.bsk(), K.ksk())
+    rng = np.random.default_rng(12)
+    bits0 = rng.integers(0, 2, size=W).astype(np.uint64)
+    w = eng.wires(3 * W)
+    w.write_rows(0, K.encrypt_batch(bits0 * np.uint64(K.delta()), 660000, big=1))
+    tabs = rng.integers(1, 15, size=(2, W)).astype(np.uint64)
+    ins = rng.integers(0, W, size=(2, 2, W))
+    lv = [E.make_gates([E.LUT] * W, b * W + ins[b, 0], b * W + ins[b, 1], (b + 1) * W + np.arange(W), lut=tabs[b], arity=[2] * W)
+          for b in range(2)]
+    # block 0 -> 1 -> 2, then 1 -> 2 again and again (level 2's outputs are never fed back, the inputs stay valid bits)
+    def step(i):
+        eng.eval_level(w, lv[0] if i == 0 else lv[1])
+    for i in range(warmup):
+        step(i)
+    eng.sync()
+    st0 = eng.stats()
+    t0 = time.perf_counter()
+    for i in range(steps):
+        step(1)
+    eng.sync()
+    wall = time.perf_counter() - t0
+    st1 = eng.stats()
+    pbs_ms = (st1["pbs_ms_total"] - st0["pbs_ms_total"]) / steps
+    ks_ms = (st1["ks_ms_total"] - st0["ks_ms_total"]) / steps
+    b1 = (tabs[0] >> (2 * bits0[ins[0, 0]] + bits0[ins[0, 1]])) & np.uint64(1)
+    b2 = (tabs[1] >> (2 * b1[ins[1, 0]] + b1[ins[1, 1]])) & np.uint64(1)
+    out = np.zeros((1024, eng.ct_words), dtype=eng.dtype)
+    w.read_rows(2 * W, out)
+    d = K.delta()
+    dec = ((K.phase_batch(out, big=1) + np.uint64(d // 2)) // np.uint64(d)) % np.uint64(K.P.msg_mod)
+    ok = bool(np.array_equal(dec, b2[:1024]))
+    if not ok:
+        raise SystemExit("bench.py: shortint leg %s decrypts wrong" % name)
+    P = K.params
+    flops = W * P["n"] * f_cmux(P["k"], P["pbs_level"], P["N"])
+    ach = flops / (pbs_ms * 1e-3) / 1e12
+    w.close(); eng.close()
+    return {"params": name, "luts_per_level": W, "pbs_per_s": W / ((pbs_ms + ks_ms) * 1e-3), "wall_pbs_per_s": W * steps / wall,
+            "pbs_kernel_ms": pbs_ms, "ks_kernel_ms": ks_ms, "mflop_per_pbs": flops / W / 1e6, "achieved_tflops": ach,
+            "frac_of_fp64_peak": ach / fp64_peak, "outputs_verified": ok}
+
+
 # ---------------------------------------------------------------- GPU arm
 def main():
     ap = argparse.ArgumentParser()
@@ -302,6 +359,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-latency", action="store_true", help="skip the c7552 gates-mode latency leg")
+    ap.add_argument("--only-shortint", action="store_true", help="run only the LUT-mode throughput legs (kernel A/B runs)")
+    ap.add_argument("--no-shortint", action="store_true", help="skip the LUT-mode (u64 parameter sets) throughput legs")
     ap.add_argument("--single-process", action="store_true",
                     help="drive all --gpus devices from THIS process through hb_ctx_create_multi (level sharding and the NVLink "
                          "exchange inside the engine) instead of one torchrun rank per GPU with NCCL")
@@ -339,6 +398,12 @@ def main():
     assert W % world == 0, "the bench level width must divide by the number of GPUs"
     g0, Wr = shard.level_slice(W, world, rank)
 
+    if args.only_shortint:
+        e0 = helm_b200.Engine(O.PARAM_SETS["toy32"], device=local)
+        peak = e0.fp64_peak_tflops()
+        e0.close()
+        emit_line({"lut_mode_throughput": [shortint_leg(nm, local, peak) for nm in ("shortint_m1c1", "shortint_m2c2")], "fp64_peak": peak})
+        return
     K = O.Keys(PARAM_SET, seed=3)
     eng = helm_b200.Engine(K.params, device=local, devices=group)
     eng.load_keys(K.bsk(), K.ksk())
@@ -494,12 +559,16 @@ def main():
 
     # ---- BASELINE.json metric, second half: c7552 gates-mode end-to-end latency (configs[1]) through the host library
     # (Yosys netlist -> restated preprocessor -> levelizer -> one hb_eval_level per level), N = 1 only
-    c7552 = c7552_lut = None
+    c7552 = c7552_lut = c880 = None
     if rank == 0 and world == 1 and not group and not args.no_latency:
         c7552 = iscas_latency("c7552", local)
         if c7552 is not None and not args.no_cpu:
             c7552.update(iscas_cpu_latency("c7552"))
         c7552_lut = iscas_latency("c7552_lut_4", local, "shortint_m2c2")
+        c880 = iscas_latency("c880", local)
+    shortint = None
+    if rank == 0 and world == 1 and not group and not args.no_shortint:
+        shortint = [shortint_leg(nm, local, fp64_peak) for nm in ("shortint_m1c1", "shortint_m2c2")]
 
     if rank == 0:
         value = W * args.steps / (ms_total * 1e-3)
@@ -527,7 +596,8 @@ def main():
                              "flops_per_launch": flops_per_launch, "kernel_ms": pbs_ms, "ks_kernel_ms": ks_ms, "gap_ms": gap_ms, "host_enqueue_ms": enqueue_ms,
                              "hbm_floor_ms": 1e3 * (bsk_bytes + 3.0 * Wr * words * 4) / (hbm_peak_gbs() * 1e9)},
                 "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
-                "verified": verified, "c7552_gates_mode": c7552, "c7552_lut_mode": c7552_lut}
+                "verified": verified, "c7552_gates_mode": c7552, "c880_gates_mode": c880, "c7552_lut_mode": c7552_lut,
+                "lut_mode_throughput": shortint}
         if group:
             line["multi"] = {k: st1[k] for k in ("n_devices", "sharded_levels", "push_bytes")}
         emit_line(line)

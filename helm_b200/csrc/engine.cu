@@ -86,7 +86,7 @@ struct hb_ctx {
     bool have_params = false, have_bsk = false, have_ksk = false;
     int shape = -1;                        // index into the kernel shape table
     DevBuf bsk_f, ksk, wtab;               // resident keys
-    DevBuf ksk_planes, ks_dig; int ksk_npad = 0;   // byte planes of the KSK for the tensor-core keyswitch (u32, ks_level 4)
+    DevBuf ksk_planes, ks_dig; int ksk_npad = 0;   // byte planes of the KSK for the tensor-core keyswitch
     DevBuf scratch_a, scratch_b;           // PBS->KS (order 0) or KS->PBS (order 1) intermediates
     DevBuf atil;                           // switched masks of the running PBS batch (pbs16_kernel)
     DevBuf lin_stage;                      // staging rows of a linear batch with read-after-write between its jobs
@@ -275,7 +275,14 @@ const Shape g_shapes[] = {
         with_small<Inst<uint32_t, 512, 2, 3, 16, 16, 1, HB_SMALL_NT, 1, HB_STAGE_KEY>>(Inst16<uint32_t, 2, 3, 6, HB_PBS16_G, 8 / HB_PBS16_G, HB_TMEMW>::shape())),
     Inst<uint32_t, 1024, 1, 3, 16, 32, 1, 192, 2>::shape(),    // concrete-core GPU path of the reference
     // PARAM_MESSAGE_1_CARRY_1_KS_PBS / PARAM_MESSAGE_2_CARRY_1_KS_PBS
+#ifndef HB_PBS16_U64_G
+#define HB_PBS16_U64_G 2
+#endif
+#if HB_PBS16_U64_G > 0
+    with_small<Inst<uint64_t, 512, 3, 1, 16, 16, 1, 256, 1, HB_STAGE_KEY>>(Inst16<uint64_t, 3, 1, 18, HB_PBS16_U64_G, 6 / HB_PBS16_U64_G, HB_TMEMW>::shape()),
+#else
     with_small<Inst<uint64_t, 512, 3, 1, 16, 16, 1, 256, 1, HB_STAGE_KEY>>(Inst<uint64_t, 512, 3, 1, 16, 16, 2, 128, 2>::shape()),
+#endif
     // PARAM_MESSAGE_2_CARRY_2_KS_PBS
     with_small<Inst<uint64_t, 2048, 1, 1, 32, 32, 1, 256, 1, HB_STAGE_KEY>>(Inst<uint64_t, 2048, 1, 1, 32, 32, 2, 128, 1>::shape()),
 };
@@ -402,14 +409,24 @@ hb_status launch_ks(hb_ctx* c, const void* in, uint32_t in_stride, void* out, ui
     if (mma_on && c->ksk_npad && n_jobs >= (uint32_t)mma_min) {
         KsMmaArgs m;
         m.a = a; m.a.split = 1; m.planes = (const uint8_t*)c->ksk_planes.p; m.npad = c->ksk_npad;
-        const dim3 grid((n_jobs + KM_TM - 1) / KM_TM, c->ksk_npad / KM_TN);
+        const int tn = c->p.torus_bits == 32 ? KmCfg<uint32_t>::TN : KmCfg<uint64_t>::TN;
+        const dim3 grid((n_jobs + KM_TM - 1) / KM_TM, c->ksk_npad / tn);
         const uint32_t rows_pad = grid.x * KM_TM;
-        CU(c, c->ks_dig.ensure((size_t)rows_pad * a.kN * KM_L));
-        ks_digits_kernel<<<rows_pad < 65535u ? rows_pad : 65535u, 256, 0, c->stream>>>(m.a, (uint8_t*)c->ks_dig.p, rows_pad);
-        static SmemOptIn opt2;
-        const size_t smem2 = 2 * (size_t)KM_STAGE;
-        CU(c, opt2.ensure(ks_mma2_kernel, smem2));
-        ks_mma2_kernel<<<grid, KM_NT, smem2, c->stream>>>(m, (const uint8_t*)c->ks_dig.p);
+        CU(c, c->ks_dig.ensure((size_t)rows_pad * a.kN * a.level));
+        const unsigned dg = rows_pad < 65535u ? rows_pad : 65535u;
+        if (c->p.torus_bits == 32) {
+            static SmemOptIn opt2;
+            const size_t smem2 = 2 * (size_t)KmCfg<uint32_t>::STAGE;
+            CU(c, opt2.ensure(ks_mma2_kernel<uint32_t>, smem2));
+            ks_digits_kernel<uint32_t><<<dg, 256, 0, c->stream>>>(m.a, (uint8_t*)c->ks_dig.p, rows_pad);
+            ks_mma2_kernel<uint32_t><<<grid, KM_NT, smem2, c->stream>>>(m, (const uint8_t*)c->ks_dig.p);
+        } else {
+            static SmemOptIn opt3;
+            const size_t smem2 = 2 * (size_t)KmCfg<uint64_t>::STAGE;
+            CU(c, opt3.ensure(ks_mma2_kernel<uint64_t>, smem2));
+            ks_digits_kernel<uint64_t><<<dg, 256, 0, c->stream>>>(m.a, (uint8_t*)c->ks_dig.p, rows_pad);
+            ks_mma2_kernel<uint64_t><<<grid, KM_NT, smem2, c->stream>>>(m, (const uint8_t*)c->ks_dig.p);
+        }
         CU(c, cudaGetLastError());
         c->stats.kernel_launches++;
         c->stats.kernel_launches++; c->stats.ks_count += n_jobs;
@@ -636,10 +653,13 @@ hb_status hb_load_ksk(hb_ctx* c, const void* ksk, size_t bytes) {
     CU(c, c->ksk.ensure(want));
     CU(c, cudaMemcpyAsync(c->ksk.p, ksk, want, cudaMemcpyHostToDevice, c->stream));
     c->ksk_npad = 0;
-    if (p.torus_bits == 32 && p.ks_level == KM_L && (p.k * p.N) % 32 == 0 && p.ks_base_log <= 7) {   // ks_mma_kernel.cuh
-        const int K = p.k * p.N * KM_L, npad = ((p.n + 1 + KM_TN - 1) / KM_TN) * KM_TN;
-        CU(c, c->ksk_planes.ensure((size_t)4 * npad * K));
-        ksk_planes_kernel<<<4 * c->sm_count, 256, 0, c->stream>>>((const uint32_t*)c->ksk.p, (uint8_t*)c->ksk_planes.p, p.n, K, npad);
+    // tensor-core keyswitch (ks_mma_kernel.cuh): byte planes of the key; every int32 plane sum must be exact
+    const int64_t K = (int64_t)p.k * p.N * p.ks_level;
+    if (K % KM_KC == 0 && p.ks_base_log <= 7 && K * (1ll << (p.ks_base_log - 1)) * 255 < (1ll << 31)) {
+        const int planes = p.torus_bits / 8, tn = 256 / planes, npad = ((p.n + 1 + tn - 1) / tn) * tn;
+        CU(c, c->ksk_planes.ensure((size_t)planes * npad * K));
+        if (p.torus_bits == 32) ksk_planes_kernel<uint32_t><<<4 * c->sm_count, 256, 0, c->stream>>>((const uint32_t*)c->ksk.p, (uint8_t*)c->ksk_planes.p, p.n, (int)K, npad);
+        else ksk_planes_kernel<uint64_t><<<4 * c->sm_count, 256, 0, c->stream>>>((const uint64_t*)c->ksk.p, (uint8_t*)c->ksk_planes.p, p.n, (int)K, npad);
         CU(c, cudaGetLastError());
         c->ksk_npad = npad;
     }

@@ -17,22 +17,32 @@
 
 namespace hb {
 
-constexpr int KM_TM = 64, KM_TN = 64, KM_KC = 128, KM_NT = 256, KM_PITCH = 144, KM_L = 4;
+// Generalised (round 2) to both torus widths and any ks_level: the key is split into sizeof(T) byte planes (4 for u32, 8 for
+// u64), the CTA tile is 64 gates x (256 / planes) columns so that the accumulators stay at 64 registers per thread, and the
+// planes are recombined in T.  u64 parameter sets (LUT / arithmetic mode) spent 27 % (M1C1) / 13 % (M2C2) of a wide level in the
+// IMAD keyswitch; exactness bound per plane: K * 2^(base_log-1) * 255 < 2^31 (checked on the host).
+constexpr int KM_TM = 64, KM_KC = 128, KM_NT = 256, KM_PITCH = 144;
+template <class T> struct KmCfg {
+    static constexpr int P = (int)sizeof(T);            // byte planes
+    static constexpr int TN = 256 / P;                  // output columns per CTA: 64 (u32), 32 (u64)
+    static constexpr int NB = TN / 16;                  // 8-column mma blocks per warp (2 warps across the columns)
+    static constexpr int STAGE = (KM_TM + P * TN) * KM_PITCH;      // one ring stage: A tile + P plane tiles
+};
 
 struct KsMmaArgs {
     KsArgs a;
-    const uint8_t* planes;     // [4][npad][K] bytes, K = kN * 4, k = i * 4 + level
-    int32_t npad;              // columns padded to a multiple of KM_TN (zero filled)
+    const uint8_t* planes;     // [P][npad][K] bytes, K = kN * level, k = i * level + (level index)
+    int32_t npad;              // columns padded to a multiple of the CTA tile (zero filled)
 };
 
-// KSK [kN][l][n+1] u32 -> byte planes [4][npad][K]
-__global__ void ksk_planes_kernel(const uint32_t* ksk, uint8_t* planes, int n, int K, int npad) {
+// KSK [kN][l][n+1] -> byte planes [P][npad][K]
+template <class T> __global__ void ksk_planes_kernel(const T* ksk, uint8_t* planes, int n, int K, int npad) {
     const size_t total = (size_t)npad * K;
     for (size_t x = (size_t)blockIdx.x * blockDim.x + threadIdx.x; x < total; x += (size_t)gridDim.x * blockDim.x) {
         const int k = (int)(x % K), col = (int)(x / K);
-        const uint32_t w = col <= n ? ksk[(size_t)k * (n + 1) + col] : 0u;
+        const T w = col <= n ? ksk[(size_t)k * (n + 1) + col] : (T)0;
 #pragma unroll
-        for (int p = 0; p < 4; ++p) planes[((size_t)p * npad + col) * K + k] = (uint8_t)(w >> (8 * p));
+        for (int p = 0; p < (int)sizeof(T); ++p) planes[((size_t)p * npad + col) * K + k] = (uint8_t)(w >> (8 * p));
     }
 }
 
@@ -45,50 +55,62 @@ __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
 }
 
-// digits of every mask word of every job, tfhe-rs SignedDecomposer (App. A.3); rows beyond n_jobs are zero
-__global__ void __launch_bounds__(256) ks_digits_kernel(const KsArgs A, uint8_t* dig, uint32_t rows_pad) {
-    const int kN = A.kN, BL = A.base_log, tot = BL * KM_L;
-    const uint32_t mask = (1u << BL) - 1;
-    const uint32_t* in = reinterpret_cast<const uint32_t*>(A.in);
+// digits of every mask word of every job, tfhe-rs SignedDecomposer (App. A.3), int8 at [g][i * level + l]; rows beyond n_jobs are zero
+template <class T> __global__ void __launch_bounds__(256) ks_digits_kernel(const KsArgs A, uint8_t* dig, uint32_t rows_pad) {
+    constexpr int BITS = (int)sizeof(T) * 8;
+    const int kN = A.kN, BL = A.base_log, L = A.level, tot = BL * L;
+    const T mask = (((T)1) << BL) - 1;
+    const T* in = reinterpret_cast<const T*>(A.in);
     for (uint32_t g = blockIdx.x; g < rows_pad; g += gridDim.x) {
         KsJob j = {{0, 0, 0, 0}, {0, 0, 0, 0}, 0, 0, 0};
         if (g < A.n_jobs) j = A.jobs[g];
-        uint32_t* row = reinterpret_cast<uint32_t*>(dig + (size_t)g * kN * KM_L);
+        uint8_t* row = dig + (size_t)g * kN * L;
         for (int i = threadIdx.x; i < kN; i += blockDim.x) {
-            uint32_t v = 0;
+            T v = 0;
 #pragma unroll
             for (int s = 0; s < 4; ++s)
-                if (j.c[s]) v += (uint32_t)j.c[s] * in[(size_t)j.src[s] * A.in_stride + i];
-            uint32_t state = v;
-            if (tot < 32) {
-                state = v >> (32 - tot - 1);
+                if (j.c[s]) v += (T)(int64_t)j.c[s] * in[(size_t)j.src[s] * A.in_stride + i];
+            T state = v;
+            if (tot < BITS) {
+                state = v >> (BITS - tot - 1);
                 state = (state + 1) >> 1;
-                state &= (1u << tot) - 1;
+                state &= (((T)1) << tot) - 1;
             }
-            uint32_t packed = 0;
+            if (L == 4) {                                                   // the common shape: one 32-bit store
+                uint32_t packed = 0;
 #pragma unroll
-            for (int l = KM_L - 1; l >= 0; --l) {
-                uint32_t res = state & mask;
-                state >>= BL;
-                uint32_t carry = ((res - 1) | state) & res;
-                carry >>= (BL - 1);
-                state += carry;
-                packed |= (uint32_t)(uint8_t)(int8_t)((int32_t)res - (int32_t)(carry << BL)) << (8 * l);
+                for (int l = 3; l >= 0; --l) {
+                    T res = state & mask;
+                    state >>= BL;
+                    T carry = ((res - 1) | state) & res;
+                    carry >>= (BL - 1);
+                    state += carry;
+                    packed |= (uint32_t)(uint8_t)(int8_t)((int32_t)res - (int32_t)(carry << BL)) << (8 * l);
+                }
+                reinterpret_cast<uint32_t*>(row)[i] = packed;
+            } else {
+                for (int l = L - 1; l >= 0; --l) {
+                    T res = state & mask;
+                    state >>= BL;
+                    T carry = ((res - 1) | state) & res;
+                    carry >>= (BL - 1);
+                    state += carry;
+                    row[(size_t)i * L + l] = (uint8_t)(int8_t)((int32_t)res - (int32_t)(carry << BL));
+                }
             }
-            row[i] = packed;
         }
     }
 }
 
-constexpr int KM_STAGE = (KM_TM + 4 * KM_TN) * KM_PITCH;      // one ring stage: A tile + 4 plane tiles
-
-__global__ void __launch_bounds__(KM_NT, 2) ks_mma2_kernel(const KsMmaArgs P, const uint8_t* dig) {
+template <class T> __global__ void __launch_bounds__(KM_NT, 2) ks_mma2_kernel(const KsMmaArgs P, const uint8_t* dig) {
+    using C = KmCfg<T>;
+    constexpr int NP = C::P, TN = C::TN, NB = C::NB;
     const KsArgs& A = P.a;
     extern __shared__ __align__(16) unsigned char km_smem[];
     __shared__ KsJob jobs[KM_TM];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int n = A.n, kN = A.kN, K = kN * KM_L;
-    const int job0 = blockIdx.x * KM_TM, col0 = blockIdx.y * KM_TN;
+    const int n = A.n, kN = A.kN, K = kN * A.level;
+    const int job0 = blockIdx.x * KM_TM, col0 = blockIdx.y * TN;
     const int njob = min(KM_TM, (int)A.n_jobs - job0);
     if (tid < KM_TM) {
         KsJob j = {{0, 0, 0, 0}, {0, 0, 0, 0}, 0, 0, 0};
@@ -96,25 +118,25 @@ __global__ void __launch_bounds__(KM_NT, 2) ks_mma2_kernel(const KsMmaArgs P, co
         jobs[tid] = j;
     }
     const int wm = warp & 3, wn = warp >> 2;
-    int acc[4][4][4];
+    int acc[NB][NP][4];
 #pragma unroll
-    for (int nb = 0; nb < 4; ++nb)
+    for (int nb = 0; nb < NB; ++nb)
 #pragma unroll
-        for (int p = 0; p < 4; ++p)
+        for (int p = 0; p < NP; ++p)
 #pragma unroll
             for (int e = 0; e < 4; ++e) acc[nb][p][e] = 0;
     const uint32_t sm_addr = (uint32_t)__cvta_generic_to_shared(km_smem);
     auto issue = [&](int k0, int stage) {
-        const uint32_t base = sm_addr + (uint32_t)stage * KM_STAGE;
+        const uint32_t base = sm_addr + (uint32_t)stage * C::STAGE;
 #pragma unroll
         for (int r = 0; r < 2; ++r) {                                   // A: 64 rows x 128 bytes
             const int q = tid + r * KM_NT, row = q >> 3, part = q & 7;
             cp_async16(base + (uint32_t)(row * KM_PITCH + part * 16), dig + (size_t)(job0 + row) * K + k0 + part * 16);
         }
 #pragma unroll
-        for (int r = 0; r < 8; ++r) {                                   // B: 4 planes x 64 columns x 128 bytes
-            const int q = tid + r * KM_NT, p = q >> 9, col = (q >> 3) & 63, part = q & 7;
-            cp_async16(base + (uint32_t)((KM_TM + p * KM_TN + col) * KM_PITCH + part * 16),
+        for (int r = 0; r < 8; ++r) {                                   // B: P planes x TN columns x 128 bytes = 2048 16-byte parts
+            const int q = tid + r * KM_NT, pc = q >> 3, part = q & 7, p = pc / TN, col = pc % TN;
+            cp_async16(base + (uint32_t)((KM_TM + pc) * KM_PITCH + part * 16),
                        P.planes + ((size_t)p * P.npad + col0 + col) * K + k0 + part * 16);
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
@@ -125,7 +147,7 @@ __global__ void __launch_bounds__(KM_NT, 2) ks_mma2_kernel(const KsMmaArgs P, co
         if (ch + 1 < nchunk) { issue((ch + 1) * KM_KC, (ch + 1) & 1); asm volatile("cp.async.wait_group 1;" ::: "memory"); }
         else asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncthreads();
-        const unsigned char* As = km_smem + (ch & 1) * KM_STAGE;
+        const unsigned char* As = km_smem + (ch & 1) * C::STAGE;
         const unsigned char* Bs = As + KM_TM * KM_PITCH;
 #pragma unroll
         for (int ks = 0; ks < KM_KC / 32; ++ks) {
@@ -136,37 +158,38 @@ __global__ void __launch_bounds__(KM_NT, 2) ks_mma2_kernel(const KsMmaArgs P, co
             a[2] = *reinterpret_cast<const uint32_t*>(ap + 16);
             a[3] = *reinterpret_cast<const uint32_t*>(ap + 8 * KM_PITCH + 16);
 #pragma unroll
-            for (int p = 0; p < 4; ++p)
+            for (int p = 0; p < NP; ++p)
 #pragma unroll
-                for (int nb = 0; nb < 4; ++nb) {
-                    const unsigned char* bp = Bs + (p * KM_TN + wn * 32 + nb * 8 + (lane >> 2)) * KM_PITCH + ks * 32 + (lane & 3) * 4;
+                for (int nb = 0; nb < NB; ++nb) {
+                    const unsigned char* bp = Bs + (p * TN + wn * (TN / 2) + nb * 8 + (lane >> 2)) * KM_PITCH + ks * 32 + (lane & 3) * 4;
                     mma_s8u8(acc[nb][p], a, *reinterpret_cast<const uint32_t*>(bp), *reinterpret_cast<const uint32_t*>(bp + 16));
                 }
         }
         __syncthreads();
     }
-    const uint32_t* in = reinterpret_cast<const uint32_t*>(A.in);
-    uint32_t* out = reinterpret_cast<uint32_t*>(A.out);
+    const T* in = reinterpret_cast<const T*>(A.in);
+    T* out = reinterpret_cast<T*>(A.out);
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
         const int g = wm * 16 + (lane >> 2) + 8 * h;
         if (g >= njob) continue;
         const KsJob& j = jobs[g];
-        uint32_t* o = out + (size_t)j.dst * A.out_stride;
+        T* o = out + (size_t)j.dst * A.out_stride;
 #pragma unroll
-        for (int nb = 0; nb < 4; ++nb)
+        for (int nb = 0; nb < NB; ++nb)
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
-                const int c = col0 + wn * 32 + nb * 8 + (lane & 3) * 2 + e;
+                const int c = col0 + wn * (TN / 2) + nb * 8 + (lane & 3) * 2 + e;
                 if (c > n) continue;
-                const uint32_t sum = (uint32_t)acc[nb][0][2 * h + e] + ((uint32_t)acc[nb][1][2 * h + e] << 8) +
-                                     ((uint32_t)acc[nb][2][2 * h + e] << 16) + ((uint32_t)acc[nb][3][2 * h + e] << 24);
-                uint32_t v = 0;
+                T sum = 0;
+#pragma unroll
+                for (int p = 0; p < NP; ++p) sum += (T)(int64_t)acc[nb][p][2 * h + e] << (8 * p);    // wraps like the T-wide product
+                T v = 0;
                 if (c == n) {
 #pragma unroll
                     for (int s = 0; s < 4; ++s)
-                        if (j.c[s]) v += (uint32_t)j.c[s] * in[(size_t)j.src[s] * A.in_stride + kN];
-                    v += (uint32_t)j.cst;
+                        if (j.c[s]) v += (T)(int64_t)j.c[s] * in[(size_t)j.src[s] * A.in_stride + kN];
+                    v += (T)j.cst;
                 }
                 o[c] = v - sum;
             }

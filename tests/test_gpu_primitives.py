@@ -20,6 +20,22 @@ def test_keyswitch_bit_exact(name, keys_factory, engine_factory):
         assert np.array_equal(got[i], K.keyswitch(cts[i])), "keyswitch row %d differs" % i
 
 
+@pytest.mark.parametrize("name", ["toy32", "boolean_default", "concrete_gpu", "toy64", "toy64b", "shortint_m1c1", "shortint_m2c2"])
+def test_keyswitch_wide_batch_tensor_core_bit_exact(name, keys_factory, engine_factory):
+    """Batches from 96 rows on run the int8 tensor-core keyswitch (ks_mma_kernel.cuh: byte planes of the key, 4 for the u32
+    torus and 8 for u64, any ks_level): word for word equal to the oracle, ragged against the 64-row tile, random full-range
+    inputs (every digit value and every carry chain of the signed decomposition occurs)."""
+    K, eng = keys_factory(name), engine_factory(name)
+    rng = np.random.default_rng(2)
+    cnt = 203
+    info = np.iinfo(K.dtype)
+    cts = rng.integers(0, info.max, size=(cnt, K.kN + 1), dtype=K.dtype, endpoint=True)
+    cts[0, :] = 0; cts[1, :] = info.max; cts[2, :] = info.max // 2 + 1          # edge rows
+    got = eng.keyswitch_batch(cts)
+    for i in range(cnt):
+        assert np.array_equal(got[i], K.keyswitch(cts[i])), "keyswitch row %d differs" % i
+
+
 @pytest.mark.parametrize("name", U32_SETS)
 def test_pbs_bit_exact_u32(name, keys_factory, engine_factory, oracle_mod):
     """u32 torus: the f64 FFT external product rounds to the exact integer negacyclic product,
