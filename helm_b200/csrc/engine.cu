@@ -1296,3 +1296,84 @@ extern "C" hb_status hb_ctx_create_multi(const int32_t* devices, int32_t n_devic
     *out = g;
     return HB_OK;
 }
+
+// ================================================================ keyswitch without any allocation
+// Added; it has no counterpart in the reference.  For callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it): the tensor-core keyswitch of ks_mma_kernel.cuh
+// needs two scratch arrays -- the identity job descriptors and the int8 digit matrix [rows][kN * ks_level] -- and here both live in
+// ONE file-scope device array of fixed size instead of the context's growable buffers.  Every GPU that loads the library holds
+// HB_NOALLOC_SCRATCH_BYTES until exit; every call (of every context on that device) shares it, so calls that overlap on the GPU
+// race; it keeps the previous call's contents, and each call rewrites every job and digit row it reads (rows up to the padded
+// tile count are zeroed by the digit kernel), so nothing needs to start at zero.
+namespace {
+constexpr size_t NOALLOC_JOB_BYTES = 64 * 1024;                       // 1365 KsJob (48 B): bounds the row count together with the digits
+static_assert(HB_NOALLOC_SCRATCH_BYTES > NOALLOC_JOB_BYTES, "scratch layout");
+static __device__ __align__(256) unsigned char g_noalloc_scratch[HB_NOALLOC_SCRATCH_BYTES];
+
+// identity jobs (row i -> row i) written straight into the static array: device code may name it directly
+__global__ void noalloc_jobs_kernel(uint32_t rows) {
+    KsJob* jobs = reinterpret_cast<KsJob*>(g_noalloc_scratch);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < rows; i += gridDim.x * blockDim.x) {
+        KsJob k = {{i, 0, 0, 0}, {1, 0, 0, 0}, 0, i, 0};
+        jobs[i] = k;
+    }
+}
+
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol: its device address is asked for once per device, with that
+// device current, and cached.
+std::atomic<unsigned char*> g_noalloc_ptr[64];
+cudaError_t noalloc_scratch_ptr(int device, unsigned char** out) {
+    if (device < 0 || device >= 64) return cudaErrorInvalidDevice;
+    unsigned char* p = g_noalloc_ptr[device].load(std::memory_order_acquire);
+    if (!p) {
+        void* q = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&q, g_noalloc_scratch);
+        if (e != cudaSuccess) return e;
+        p = static_cast<unsigned char*>(q);
+        g_noalloc_ptr[device].store(p, std::memory_order_release);
+    }
+    *out = p;
+    return cudaSuccess;
+}
+
+template <class T> hb_status ks_noalloc_t(hb_ctx* c, const void* in_dev, uint32_t count, void* out_dev, unsigned char* scratch) {
+    using Cfg = KmCfg<T>;
+    KsMmaArgs m;
+    KsArgs& a = m.a;
+    a.in = in_dev; a.in_stride = big_words(c); a.out = out_dev; a.out_stride = small_words(c);
+    a.jobs = reinterpret_cast<const KsJob*>(scratch); a.n_jobs = count;
+    a.ksk = c->ksk.p; a.n = c->p.n; a.kN = c->p.k * c->p.N; a.base_log = c->p.ks_base_log; a.level = c->p.ks_level; a.split = 1;
+    m.planes = (const uint8_t*)c->ksk_planes.p; m.npad = c->ksk_npad;
+    uint8_t* dig = scratch + NOALLOC_JOB_BYTES;
+    const dim3 grid((count + KM_TM - 1) / KM_TM, c->ksk_npad / Cfg::TN);
+    const uint32_t rows_pad = grid.x * KM_TM;
+    static SmemOptIn opt;
+    const size_t smem = 2 * (size_t)Cfg::STAGE;
+    CU(c, opt.ensure(ks_mma2_kernel<T>, smem));
+    noalloc_jobs_kernel<<<(count + 255) / 256, 256, 0, c->stream>>>(count);
+    ks_digits_kernel<T><<<rows_pad, 256, 0, c->stream>>>(a, dig, rows_pad);
+    ks_mma2_kernel<T><<<grid, KM_NT, smem, c->stream>>>(m, dig);
+    CU(c, cudaGetLastError());
+    c->stats.kernel_launches += 3; c->stats.ks_count += count;
+    return HB_OK;
+}
+}  // namespace
+
+extern "C" hb_status hb_keyswitch_batch_noalloc(hb_ctx* c, const void* lwe_in_dev, uint32_t count, void* lwe_out_dev) {
+    if (c && c->is_group()) return lift(c, c->subs[0], hb_keyswitch_batch_noalloc(c->subs[0], lwe_in_dev, count, lwe_out_dev));
+    if (hb_status s = check_ready(c)) return s;
+    if (!lwe_in_dev || !lwe_out_dev) return fail(c, HB_ERR_ARG, "hb_keyswitch_batch_noalloc: null buffer");
+    if (!count) return HB_OK;
+    if (!c->ksk_npad) return fail(c, HB_ERR_UNSUPPORTED, "hb_keyswitch_batch_noalloc: this parameter set has no tensor-core keyswitch (the scratch-using kernel)");
+    const size_t row_bytes = (size_t)c->p.k * c->p.N * c->p.ks_level;                     // int8 digits per row
+    size_t max_rows = (HB_NOALLOC_SCRATCH_BYTES - NOALLOC_JOB_BYTES) / row_bytes / KM_TM * KM_TM;   // whole 64-row tiles
+    if (max_rows > NOALLOC_JOB_BYTES / sizeof(KsJob)) max_rows = NOALLOC_JOB_BYTES / sizeof(KsJob) / KM_TM * KM_TM;
+    if (count > max_rows)
+        return fail(c, HB_ERR_ARG, "hb_keyswitch_batch_noalloc: count " + std::to_string(count) + " exceeds the static scratch (" +
+                    std::to_string(HB_NOALLOC_SCRATCH_BYTES) + " bytes): at most " + std::to_string(max_rows) + " rows for this parameter set");
+    CU(c, cudaSetDevice(c->device));
+    unsigned char* scratch = nullptr;
+    CU(c, noalloc_scratch_ptr(c->device, &scratch));
+    return c->p.torus_bits == 32 ? ks_noalloc_t<uint32_t>(c, lwe_in_dev, count, lwe_out_dev, scratch)
+                                 : ks_noalloc_t<uint64_t>(c, lwe_in_dev, count, lwe_out_dev, scratch);
+}

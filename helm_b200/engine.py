@@ -47,7 +47,8 @@ assert SOP_DTYPE.itemsize == 40 and SOP_DTYPE.fields["in"][1] == 8 and SOP_DTYPE
 EXPORTS = ["hb_ctx_create", "hb_ctx_create_multi", "hb_ctx_destroy", "hb_last_error", "hb_set_params", "hb_load_bsk", "hb_load_ksk",
            "hb_wires_create", "hb_wires_attach", "hb_wires_destroy", "hb_ct_words", "hb_wire_stride",
            "hb_wires_device_ptr", "hb_wires_write", "hb_wires_read", "hb_wires_write_rows", "hb_wires_read_rows", "hb_wires_set_trivial", "hb_eval_level", "hb_eval_shortint_ops",
-           "hb_sync", "hb_stats", "hb_stream", "hb_pbs_batch", "hb_keyswitch_batch", "hb_measure_fp64_peak"]
+           "hb_sync", "hb_stats", "hb_stream", "hb_pbs_batch", "hb_keyswitch_batch", "hb_keyswitch_batch_noalloc",
+           "hb_measure_fp64_peak"]
 
 _LIB = None
 
@@ -94,6 +95,7 @@ def lib():
         L.hb_stream.argtypes = [vp]
         L.hb_pbs_batch.argtypes = [vp, vp, vp, i32, u32, vp]
         L.hb_keyswitch_batch.argtypes = [vp, vp, u32, vp]
+        L.hb_keyswitch_batch_noalloc.argtypes = [vp, vp, u32, vp]
         L.hb_measure_fp64_peak.argtypes = [vp, C.POINTER(C.c_double)]
         _LIB = L
     return _LIB
@@ -202,6 +204,11 @@ class Engine:
         out = np.zeros((lwe_in.shape[0], self.n + 1), dtype=self.dtype)
         self._ck(self.L.hb_keyswitch_batch(self.h, _ptr(lwe_in), lwe_in.shape[0], _ptr(out)), "hb_keyswitch_batch")
         return out
+
+    def keyswitch_batch_noalloc(self, in_dev_ptr, count, out_dev_ptr):
+        """hb_keyswitch_batch_noalloc: device pointers in and out, static scratch, no allocation; asynchronous (sync() after)."""
+        self._ck(self.L.hb_keyswitch_batch_noalloc(self.h, C.c_void_p(in_dev_ptr), count, C.c_void_p(out_dev_ptr)),
+                 "hb_keyswitch_batch_noalloc")
 
     def fp64_peak_tflops(self):
         v = C.c_double()

@@ -142,6 +142,18 @@ hb_status hb_pbs_batch(hb_ctx*, const void* lwe_in, const void* test_vector_bodi
                        uint32_t count, void* lwe_out);
 /* lwe_in: count x (kN+1); out: count x (n+1) */
 hb_status hb_keyswitch_batch(hb_ctx*, const void* lwe_in, uint32_t count, void* lwe_out);
+/* Keyswitch of `count` rows that allocates NOTHING (no cudaMalloc / cudaFree / allocating library call), for callers under CUDA
+ * graph capture, in tight serving loops or in harnesses that forbid allocation.  No counterpart in the reference.
+ * lwe_in_dev: count x (kN+1) packed torus words in DEVICE memory; lwe_out_dev: count x (n+1) in
+ * DEVICE memory (the caller's buffers; the call is asynchronous on the context's stream -- hb_sync before reading, and make the
+ * inputs visible to that stream first).  Same arithmetic as hb_keyswitch_batch (bit-identical).  The scratch of the tensor-core
+ * keyswitch (job descriptors + int8 digit matrix) lives in one static device array of HB_NOALLOC_SCRATCH_BYTES that every GPU
+ * loading the library holds until exit: count is limited to floor((HB_NOALLOC_SCRATCH_BYTES - 64 KiB) / (kN * ks_level)) rounded
+ * down to a multiple of 64 and to at most 1344 rows (boolean default: 1344, shortint M2C2: 768); larger counts return HB_ERR_ARG with
+ * the limit in hb_last_error.  All calls on one device share that array: calls that overlap on the GPU (two contexts / streams) race.
+ * Parameter sets without the tensor-core keyswitch return HB_ERR_UNSUPPORTED. */
+#define HB_NOALLOC_SCRATCH_BYTES (8u << 20)
+hb_status hb_keyswitch_batch_noalloc(hb_ctx*, const void* lwe_in_dev, uint32_t count, void* lwe_out_dev);
 /* measured FP64 FMA throughput of this device in TFLOP/s (register-resident DFMA loop) */
 hb_status hb_measure_fp64_peak(hb_ctx*, double* tflops);
 
