@@ -20,7 +20,7 @@ class Params(C.Structure):
                 ("pbs_base_log", C.c_int32), ("pbs_level", C.c_int32),
                 ("ks_base_log", C.c_int32), ("ks_level", C.c_int32),
                 ("torus_bits", C.c_int32), ("order", C.c_int32),
-                ("msg_mod", C.c_int32), ("carry_mod", C.c_int32),
+                ("msg_mod", C.c_int32), ("carry_mod", C.c_int32), ("grouping", C.c_int32),
                 ("lwe_std", C.c_double), ("glwe_std", C.c_double)]
 
 
@@ -42,6 +42,13 @@ PARAM_SETS = {
     "concrete_gpu": dict(n=512, k=1, N=1024, pbs_base_log=7, pbs_level=3, ks_base_log=2, ks_level=8,
                          torus_bits=32, order=0, msg_mod=0, carry_mod=0,
                          lwe_std=2.0 ** -25, glwe_std=2.0 ** -25),
+    # PARAM_MULTI_BIT_MESSAGE_2_CARRY_2_GROUP_3_KS_PBS: the reference's arithmetic-mode set (src/bin/helm.rs:81-86); multi-bit
+    # blind rotation, grouping factor 3 (values as recalled in SURVEY.md section 8 / App. A.1, medium confidence)
+    "shortint_multibit_m2c2_g3": dict(n=888, k=1, N=2048, pbs_base_log=21, pbs_level=1, ks_base_log=4, ks_level=4,
+                                      torus_bits=64, order=1, msg_mod=4, carry_mod=4, grouping=3,
+                                      lwe_std=6.125031601933181e-7, glwe_std=2.9403601535432533e-16),
+    "toy64m": dict(n=36, k=1, N=2048, pbs_base_log=21, pbs_level=1, ks_base_log=4, ks_level=4,
+                   torus_bits=64, order=1, msg_mod=4, carry_mod=4, grouping=3, lwe_std=2.0 ** -24, glwe_std=2.0 ** -52),
     # small set for fast CPU tests (NOT secure; same code paths, k=2 / l=3 like boolean_default)
     "toy32": dict(n=48, k=2, N=512, pbs_base_log=6, pbs_level=3, ks_base_log=3, ks_level=4,
                   torus_bits=32, order=0, msg_mod=0, carry_mod=0, lwe_std=2.0 ** -20, glwe_std=2.0 ** -28),
@@ -114,7 +121,8 @@ class Keys:
         if isinstance(params, str):
             params = PARAM_SETS[params]
         self.params = dict(params)
-        self.P = Params(**params)
+        self.params.setdefault("grouping", 0)
+        self.P = Params(**self.params)
         self.L = lib()
         self.h = self.L.orc_keygen(C.byref(self.P), seed)
         self.dtype = np.uint32 if self.P.torus_bits == 32 else np.uint64
@@ -135,7 +143,9 @@ class Keys:
         return np.frombuffer(buf, dtype=self.dtype)
 
     def bsk(self):
-        return self._view(self.L.orc_bsk).reshape(self.n, self.P.pbs_level, self.k + 1, self.k + 1, self.N)
+        g = self.P.grouping
+        lead = (self.n // g) * (1 << g) if g > 1 else self.n       # multi-bit: [group][pattern] flattened
+        return self._view(self.L.orc_bsk).reshape(lead, self.P.pbs_level, self.k + 1, self.k + 1, self.N)
 
     def ksk(self):
         return self._view(self.L.orc_ksk).reshape(self.kN, self.P.ks_level, self.n + 1)

@@ -173,15 +173,24 @@ template <class T> void keygen_t(orc_keys* K, uint64_t seed) {
     K->lwe_sk.resize(n); K->glwe_sk.resize((size_t)k * N);
     for (auto& b : K->lwe_sk) b = r.next() & 1;
     for (auto& b : K->glwe_sk) b = r.next() & 1;
-    // BSK: GGSW(s_i), layout [i][level][row][poly][N]
+    // BSK: GGSW(s_i), layout [i][level][row][poly][N]; multi-bit (grouping g > 1): GGSW(prod_j (bit_j(q) ? s_j : 1 - s_j)) for
+    // every group of g key bits and every pattern q < 2^g, layout [group][q][level][row][poly][N]
     const size_t row_words = (size_t)(k + 1) * N;
-    K->bsk.assign((size_t)n * l * (k + 1) * row_words * sizeof(T), 0);
+    const int grp = p.grouping > 1 ? p.grouping : 1, pats = grp > 1 ? (1 << grp) : 1;
+    const int n_ggsw = grp > 1 ? (n / grp) * pats : n;
+    K->bsk.assign((size_t)n_ggsw * l * (k + 1) * row_words * sizeof(T), 0);
     T* bsk = (T*)K->bsk.data();
     // independent stream per GGSW so the loop can run in parallel deterministically
     uint64_t base_seed = r.next();
 #pragma omp parallel for schedule(dynamic, 4)
-    for (int i = 0; i < n; ++i) {
+    for (int i = 0; i < n_ggsw; ++i) {
         Rng ri(base_seed + 0x1000003ull * (uint64_t)(i + 1));
+        int message = K->lwe_sk[grp > 1 ? 0 : i];
+        if (grp > 1) {
+            const int g0 = (i / pats) * grp, q = i % pats;
+            message = 1;
+            for (int j = 0; j < grp; ++j) message &= ((q >> j) & 1) ? K->lwe_sk[g0 + j] : 1 - K->lwe_sk[g0 + j];
+        }
         for (int lev = 1; lev <= l; ++lev) {
             for (int row = 0; row <= k; ++row) {
                 T* g = bsk + (((size_t)i * l + (lev - 1)) * (k + 1) + row) * row_words;
@@ -192,7 +201,7 @@ template <class T> void keygen_t(orc_keys* K, uint64_t seed) {
                     for (int c = 0; c < N; ++c) a[c] = (T)ri.next();
                     poly_mul_binary_acc<T>(a, K->glwe_sk.data() + (size_t)j * N, N, body);
                 }
-                if (K->lwe_sk[i]) {   // + m * q/B^lev on component `row` (after the body was formed from the mask)
+                if (message) {        // + m * q/B^lev on component `row` (after the body was formed from the mask)
                     T gad = ((T)1) << (BITS - p.pbs_base_log * lev);
                     g[(size_t)row * N] += gad;
                     // phase = body - sum A_j S_j must be E - m*g*S_row (row<k) or E + m*g (row=k):
@@ -237,9 +246,9 @@ inline int ilog2(int x) { int r = 0; while ((1 << r) < x) ++r; return r; }
 template <class T> void build_fourier(orc_keys* K) {
     if (K->fourier_ready) return;
     const orc_params& p = K->p;
-    const int n = p.n, k = p.k, N = p.N, l = p.pbs_level, M = N / 2;
+    const int N = p.N, M = N / 2;
     K->fft.init(M);
-    const size_t polys = (size_t)n * l * (k + 1) * (k + 1);
+    const size_t polys = K->bsk.size() / sizeof(T) / N;
     K->fbsk_re.resize(polys * M); K->fbsk_im.resize(polys * M);
     const T* bsk = (const T*)K->bsk.data();
     const double scale = std::ldexp(1.0, -bits_of<T>());
@@ -340,6 +349,103 @@ template <class T> void cmux_t(const orc_keys* K, int i, uint32_t a_tilde, T* ac
     }
 }
 
+// Multi-bit blind-rotation step (tfhe-rs multi_bit_blind_rotate_assign as recalled in SURVEY.md sections 0 / 8f; the crate is not
+// in /root/reference): for group `grp` with switched mask elements a[0..g), pattern q carries the monomial X^{e_q},
+// e_q = sum_{j: bit_j(q)} a_j, and   acc <- ExternalProduct( sum_q GGSW_q * X^{e_q}, acc )   -- exactly one pattern encrypts 1,
+// so the accumulator is rotated by X^{sum_j a_j s_j} with ONE external product per g key bits.
+template <class T> void multibit_step_t(const orc_keys* K, int grp, const uint32_t* a, T* acc, int mode, Scratch& sc) {
+    const orc_params& p = K->p;
+    const int k = p.k, N = p.N, l = p.pbs_level, M = N / 2, g = p.grouping, pats = 1 << g;
+    const size_t row_words = (size_t)(k + 1) * N;
+    sc.dig.resize((size_t)l * row_words * sizeof(S<T>));
+    S<T>* dig = (S<T>*)sc.dig.data();
+    S<T> d[64];
+    for (size_t c = 0; c < row_words; ++c) {
+        decompose<T>(acc[c], p.pbs_base_log, l, d);
+        for (int lev = 0; lev < l; ++lev) dig[(size_t)lev * row_words + c] = d[lev];
+    }
+    int e[64];
+    for (int q = 0; q < pats; ++q) {
+        unsigned s = 0;
+        for (int j = 0; j < g; ++j) if ((q >> j) & 1) s += a[j];
+        e[q] = (int)(s % (2u * N));
+    }
+    if (mode == ORC_EXACT) {
+        std::vector<T> res(row_words, 0);
+        const T* bsk = (const T*)K->bsk.data();
+        std::vector<T> part(N);
+        for (int q = 0; q < pats; ++q)
+            for (int j = 0; j <= k; ++j) {
+                std::fill(part.begin(), part.end(), (T)0);
+                for (int lev = 0; lev < l; ++lev)
+                    for (int r = 0; r <= k; ++r) {
+                        const S<T>* dp = dig + (size_t)lev * row_words + (size_t)r * N;
+                        const T* gp = bsk + (((((size_t)grp * pats + q) * l + lev) * (k + 1) + r) * (k + 1) + j) * N;
+                        for (int x = 0; x < N; ++x) {
+                            const T dx = (T)dp[x];
+                            if (dx == 0) continue;
+                            for (int y = 0; y < N - x; ++y) part[x + y] += dx * gp[y];
+                            for (int y = N - x; y < N; ++y) part[x + y - N] -= dx * gp[y];
+                        }
+                    }
+                // times X^{e_q}: coefficient c of the product is coefficient c - e of part (negacyclic)
+                T* o = res.data() + (size_t)j * N;
+                for (int c = 0; c < N; ++c) o[c] += rot_coef<T>(part.data(), N, c, e[q]);
+            }
+        std::memcpy(acc, res.data(), row_words * sizeof(T));
+        return;
+    }
+    const Fft& F = K->fft;
+    const int lgM = ilog2(M);
+    std::vector<double> dre((size_t)l * (k + 1) * M), dim((size_t)l * (k + 1) * M);     // spectra of the digit polynomials
+    for (int lev = 0; lev < l; ++lev)
+        for (int r = 0; r <= k; ++r) {
+            const S<T>* dp = dig + (size_t)lev * row_words + (size_t)r * N;
+            double* re = dre.data() + ((size_t)lev * (k + 1) + r) * M; double* im = dim.data() + ((size_t)lev * (k + 1) + r) * M;
+            for (int j = 0; j < M; ++j) {
+                double x = (double)dp[j], y = (double)dp[j + M];
+                re[j] = x * F.tr[j] - y * F.ti[j]; im[j] = x * F.ti[j] + y * F.tr[j];
+            }
+            F.fwd(re, im);
+        }
+    sc.ore.assign((size_t)(k + 1) * M, 0.0); sc.oim.assign((size_t)(k + 1) * M, 0.0);
+    // spectrum of X^e at frequency f (kernel e^{+2 pi i jf/M}, twist e^{+i pi j/N}): exp(i pi e (4f+1) / N); position x of the
+    // bit-reversed output order holds frequency brev(x)
+    for (int x = 0; x < M; ++x) {
+        int f = 0;
+        for (int b = 0; b < lgM; ++b) f |= ((x >> b) & 1) << (lgM - 1 - b);
+        double mr[64], mi[64];
+        for (int q = 0; q < pats; ++q) {
+            const long t = ((long)e[q] * (4L * f + 1)) % (2L * N);
+            const double ang = M_PI * (double)t / (double)N;
+            mr[q] = std::cos(ang); mi[q] = std::sin(ang);
+        }
+        for (int lev = 0; lev < l; ++lev)
+            for (int r = 0; r <= k; ++r)
+                for (int j = 0; j <= k; ++j) {
+                    double cr = 0, ci = 0;                                  // combined key entry: sum_q G_q * m_q
+                    for (int q = 0; q < pats; ++q) {
+                        const size_t poly = ((((size_t)grp * pats + q) * l + lev) * (k + 1) + r) * (k + 1) + j;
+                        const double br = K->fbsk_re[poly * M + x], bi = K->fbsk_im[poly * M + x];
+                        cr += br * mr[q] - bi * mi[q]; ci += br * mi[q] + bi * mr[q];
+                    }
+                    const double xr = dre[((size_t)lev * (k + 1) + r) * M + x], xi = dim[((size_t)lev * (k + 1) + r) * M + x];
+                    sc.ore[(size_t)j * M + x] += xr * cr - xi * ci; sc.oim[(size_t)j * M + x] += xr * ci + xi * cr;
+                }
+    }
+    const double invM = 1.0 / M;
+    for (int j = 0; j <= k; ++j) {
+        double* re = sc.ore.data() + (size_t)j * M; double* im = sc.oim.data() + (size_t)j * M;
+        F.inv(re, im);
+        T* out = acc + (size_t)j * N;
+        for (int x = 0; x < M; ++x) {
+            double zr = re[x] * invM, zi = im[x] * invM;
+            double pr = zr * F.tr[x] + zi * F.ti[x], pi = zi * F.tr[x] - zr * F.ti[x];
+            out[x] = from_torus_f64<T>(pr); out[x + M] = from_torus_f64<T>(pi);      // acc <- product (not +=)
+        }
+    }
+}
+
 template <class T> void pbs_t(const orc_keys* K, const T* in, const T* tv, T* out, int mode, Scratch& sc) {
     const orc_params& p = K->p;
     const int n = p.n, k = p.k, N = p.N, lg = ilog2(N);
@@ -349,6 +455,13 @@ template <class T> void pbs_t(const orc_keys* K, const T* in, const T* tv, T* ou
     const int a0 = (2 * N - bt) % (2 * N);            // TV * X^{-b~}
     for (int j = 0; j <= k; ++j)
         for (int c = 0; c < N; ++c) acc[(size_t)j * N + c] = rot_coef<T>(tv + (size_t)j * N, N, c, a0);
+    if (p.grouping > 1) {
+        uint32_t a[16];
+        for (int grp = 0; grp < n / p.grouping; ++grp) {
+            for (int j = 0; j < p.grouping; ++j) a[j] = modswitch1<T>(in[grp * p.grouping + j], lg) % (2u * N);
+            multibit_step_t<T>(K, grp, a, acc.data(), mode, sc);
+        }
+    } else
     for (int i = 0; i < n; ++i) cmux_t<T>(K, i, modswitch1<T>(in[i], lg), acc.data(), mode, sc);
     // sample extract coefficient 0 (App. A.5)
     for (int j = 0; j < k; ++j) {

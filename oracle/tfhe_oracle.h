@@ -46,6 +46,10 @@ typedef struct {
     int32_t order;        /* 0 = PBS then KS (ciphertexts under small key),
                              1 = KS then PBS (ciphertexts under big key) */
     int32_t msg_mod, carry_mod;   /* shortint only; 0 for boolean */
+    int32_t grouping;             /* 0 / 1: classic blind rotation (one CMUX per key bit); g > 1: multi-bit blind rotation with
+                                     grouping factor g (tfhe-rs multi_bit PBS, reference src/bin/helm.rs:81-86): the BSK holds, per group of
+                                     g key bits, 2^g GGSWs -- pattern q encrypts prod_j (bit_j(q) ? s_j : 1 - s_j) -- layout
+                                     [n/g][2^g][level][row][poly][N] */
     double lwe_std, glwe_std;     /* noise std-dev as a fraction of the torus */
 } orc_params;
 
