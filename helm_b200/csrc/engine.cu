@@ -215,6 +215,7 @@ struct Shape {
     cudaError_t (*launch)(const PbsArgs&, cudaStream_t, size_t smem);
     cudaError_t (*bsk_fft)(const void* std_bsk, double2* out, const double2* wtab, size_t polys, cudaStream_t);
     int BL = 0;                            // compile-time pbs_base_log of the instance (0: run-time)
+    int MB = 0;                            // multi-bit grouping factor of the instance (0: classic blind rotation)
     // narrow batches (<= 3 x SMs bootstraps): one gate per CTA, every transform on its own group of threads
     size_t (*small_smem)(int n) = nullptr;
     cudaError_t (*small_launch)(const PbsArgs&, cudaStream_t, size_t smem) = nullptr;
@@ -233,12 +234,12 @@ constexpr size_t PBS_DYN_SMEM_MAX = 226 * 1024;
 #ifndef HB_STAGE_KEY
 #define HB_STAGE_KEY true      // narrow-batch instances stage BSK_i in shared memory (cp.async.bulk), see pbs_kernel.cuh
 #endif
-template <class T, int N, int K, int L, int RA, int RB, int G, int NT, int MINB, bool STAGE = false>
+template <class T, int N, int K, int L, int RA, int RB, int G, int NT, int MINB, bool STAGE = false, int MB = 0>
 struct Inst {
     using C = PbsCfg<T, N, K, L, RA, RB, G>;
     static size_t smem(int n) { return STAGE ? C::smem_bytes_staged(n) : C::smem_bytes(n); }
     static cudaError_t launch(const PbsArgs& a, cudaStream_t s, size_t smem) {
-        auto kern = pbs_kernel<T, N, K, L, RA, RB, G, NT, MINB, STAGE>;
+        auto kern = pbs_kernel<T, N, K, L, RA, RB, G, NT, MINB, STAGE, MB>;
         static SmemOptIn opt;
         if (cudaError_t e = opt.ensure(kern, PBS_DYN_SMEM_MAX)) return e;
         const unsigned grid = (a.n_jobs + G - 1) / G;
@@ -250,7 +251,7 @@ struct Inst {
         bsk_fft_kernel<T, N, RA, RB><<<(unsigned)polys, RA > RB ? RA : RB, 0, s>>>((const T*)std_bsk, out, wtab, scale);
         return cudaGetLastError();
     }
-    static constexpr Shape shape() { return Shape{(int)sizeof(T) * 8, N, K, L, RA, RB, G, NT, &smem, &launch, &bsk_fft}; }
+    static constexpr Shape shape() { Shape s{(int)sizeof(T) * 8, N, K, L, RA, RB, G, NT, &smem, &launch, &bsk_fft}; s.MB = MB; return s; }
 };
 
 // N = 512 shapes run the half-warp-per-polynomial kernel (pbs16_kernel.cuh); the key transform and the Fourier key layout are shared
@@ -285,12 +286,15 @@ const Shape g_shapes[] = {
 #endif
     // PARAM_MESSAGE_2_CARRY_2_KS_PBS
     with_small<Inst<uint64_t, 2048, 1, 1, 32, 32, 1, 256, 1, HB_STAGE_KEY>>(Inst<uint64_t, 2048, 1, 1, 32, 32, 2, 128, 1>::shape()),
+    // PARAM_MULTI_BIT_MESSAGE_2_CARRY_2_GROUP_3_KS_PBS (the reference's arithmetic mode, src/bin/helm.rs:81-86): multi-bit, grouping 3
+    with_small<Inst<uint64_t, 2048, 1, 1, 32, 32, 1, 256, 1, false, 3>>(Inst<uint64_t, 2048, 1, 1, 32, 32, 2, 128, 1, false, 3>::shape()),
 };
 
 int find_shape(const hb_params& p) {
     for (size_t i = 0; i < sizeof(g_shapes) / sizeof(g_shapes[0]); ++i) {
         const Shape& s = g_shapes[i];
-        if (s.bits == p.torus_bits && s.N == p.N && s.K == p.k && s.L == p.pbs_level && (s.BL == 0 || s.BL == p.pbs_base_log)) return (int)i;
+        if (s.bits == p.torus_bits && s.N == p.N && s.K == p.k && s.L == p.pbs_level && (s.BL == 0 || s.BL == p.pbs_base_log) &&
+            s.MB == (p.grouping > 1 ? p.grouping : 0)) return (int)i;
     }
     return -1;
 }
@@ -361,6 +365,7 @@ hb_status launch_pbs(hb_ctx* c, const void* in, uint32_t in_stride, void* out, u
     PbsArgs a{};
     a.in = in; a.in_stride = in_stride; a.out = out; a.out_stride = out_stride; a.jobs = jobs; a.n_jobs = n_jobs;
     a.bsk = (const double2*)c->bsk_f.p; a.wtab = (const double2*)c->wtab.p; a.n = c->p.n; a.base_log = c->p.pbs_base_log;
+    a.roots = (const double2*)c->wtab.p + 2 * (size_t)(sh.RA * sh.RB);
     // Narrow batches are latency-bound (one bootstrap is n sequential CMUX steps, so what matters is the time of ONE step of
     // ONE CTA).
     // Measured on boolean default (tests/tools/narrow_sweep.py, ms per launch): one gate per CTA 2.87 up to 1 x SMs bootstraps;
@@ -406,7 +411,9 @@ hb_status launch_ks(hb_ctx* c, const void* in, uint32_t in_stride, void* out, ui
     // batches from ~100 jobs on the tensor cores (bit-identical; HB_KS_MMA=0 keeps the IMAD kernel)
     static const int mma_on = getenv("HB_KS_MMA") ? atoi(getenv("HB_KS_MMA")) : 1;
     static const int mma_min = getenv("HB_KS_MMA_MIN") ? atoi(getenv("HB_KS_MMA_MIN")) : 96;   // tests/tools/narrow_sweep.py: 0.050 ms up to 592 jobs, IMAD 0.044 (64) .. 0.195 (592)
-    if (mma_on && c->ksk_npad && n_jobs >= (uint32_t)mma_min) {
+    const bool too_wide = c->p.n + 1 > KS_NT * KS_QC;           // the IMAD tile covers 768 output columns: wider keys always take the tensor path
+    if (too_wide && !c->ksk_npad) return fail(c, HB_ERR_UNSUPPORTED, "keyswitch: n+1 > 768 needs the tensor-core path");
+    if (c->ksk_npad && (too_wide || (mma_on && n_jobs >= (uint32_t)mma_min))) {
         KsMmaArgs m;
         m.a = a; m.a.split = 1; m.planes = (const uint8_t*)c->ksk_planes.p; m.npad = c->ksk_npad;
         const int tn = c->p.torus_bits == 32 ? KmCfg<uint32_t>::TN : KmCfg<uint64_t>::TN;
@@ -601,7 +608,10 @@ hb_status hb_set_params(hb_ctx* c, const hb_params* p) {
     if (p->torus_bits != 32 && p->torus_bits != 64) return fail(c, HB_ERR_ARG, "torus_bits must be 32 or 64");
     const int sh = find_shape(*p);
     if (sh < 0) return fail(c, HB_ERR_UNSUPPORTED, "no sm_100a kernel instance for this (torus_bits, N, k, pbs_level)");
-    if (p->n + 1 > KS_NT * KS_QC) return fail(c, HB_ERR_UNSUPPORTED, "n+1 exceeds keyswitch tile (768)");
+    const int64_t ksK = (int64_t)p->k * p->N * p->ks_level;
+    const bool ks_mma_ok = ksK % KM_KC == 0 && p->ks_base_log <= 7 && ksK * (1ll << (p->ks_base_log - 1)) * 255 < (1ll << 31);
+    if (p->n + 1 > KS_NT * KS_QC && !ks_mma_ok) return fail(c, HB_ERR_UNSUPPORTED, "n+1 exceeds the keyswitch tile (768) and the key shape rules out the tensor-core keyswitch");
+    if (p->grouping > 1 && p->n % p->grouping) return fail(c, HB_ERR_ARG, "multi-bit: n must be a multiple of the grouping factor");
     if (p->ks_level > KS_MAXL || p->ks_base_log > 7) return fail(c, HB_ERR_UNSUPPORTED, "keyswitch decomposition too wide (level<=8, base_log<=7)");
     if (p->pbs_base_log * p->pbs_level > p->torus_bits || p->pbs_base_log > 31) return fail(c, HB_ERR_ARG, "bad PBS decomposition");
     if (p->torus_bits == 32 && p->pbs_base_log > 7) return fail(c, HB_ERR_UNSUPPORTED, "u32 torus: pbs_base_log must be <= 7 (digits are staged as bytes)");
@@ -610,10 +620,11 @@ hb_status hb_set_params(hb_ctx* c, const hb_params* p) {
     c->p = *p; c->shape = sh; c->have_params = true; c->have_bsk = c->have_ksk = false;
     const Shape& s = g_shapes[sh];
     const int M = s.RA * s.RB;
-    CU(c, c->wtab.ensure(2 * (size_t)M * sizeof(double2)));
+    CU(c, c->wtab.ensure((2 * (size_t)M + 2 * (size_t)p->N) * sizeof(double2)));
     wtab_kernel<<<(M + 255) / 256, 256, 0, c->stream>>>((double2*)c->wtab.p, s.RA, s.RB);
+    roots_kernel<<<(2 * p->N + 255) / 256, 256, 0, c->stream>>>((double2*)c->wtab.p + 2 * M, p->N);      // multi-bit monomial spectra
     CU(c, cudaGetLastError());
-    c->stats.kernel_launches++;
+    c->stats.kernel_launches += 2;
     return HB_OK;
 }
 
@@ -623,9 +634,10 @@ hb_status hb_load_bsk(hb_ctx* c, const void* bsk, size_t bytes) {
     if (!c->have_params) return fail(c, HB_ERR_STATE, "hb_set_params not called");
     CU(c, cudaSetDevice(c->device));
     const hb_params& p = c->p;
-    const size_t polys = (size_t)p.n * p.pbs_level * (p.k + 1) * (p.k + 1);
+    const size_t n_ggsw = p.grouping > 1 ? (size_t)(p.n / p.grouping) << p.grouping : (size_t)p.n;
+    const size_t polys = n_ggsw * p.pbs_level * (p.k + 1) * (p.k + 1);
     const size_t want = polys * p.N * tsize(c);
-    if (bytes != want) return fail(c, HB_ERR_ARG, "hb_load_bsk: byte size does not match [n][l][k+1][k+1][N]");
+    if (bytes != want) return fail(c, HB_ERR_ARG, "hb_load_bsk: byte size does not match [n][l][k+1][k+1][N] (multi-bit: [n/g][2^g][l][k+1][k+1][N])");
     const Shape& s = g_shapes[c->shape];
     CU(c, c->bsk_f.ensure(polys * (p.N / 2) * sizeof(double2)));
     // stage the standard-domain key in chunks, transform on device

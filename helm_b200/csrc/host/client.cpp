@@ -9,10 +9,10 @@
 namespace helm {
 
 static Params mk(const char* name, int n, int k, int N, int bl, int l, int kbl, int kl, int bits, int order, int msg, int carry,
-                 double lwe_std, double glwe_std) {
+                 double lwe_std, double glwe_std, int grouping = 0) {
     Params p; p.name = name;
     p.hb.n = n; p.hb.k = k; p.hb.N = N; p.hb.pbs_base_log = bl; p.hb.pbs_level = l; p.hb.ks_base_log = kbl; p.hb.ks_level = kl;
-    p.hb.torus_bits = bits; p.hb.order = order; p.hb.msg_mod = msg; p.hb.carry_mod = carry;
+    p.hb.torus_bits = bits; p.hb.order = order; p.hb.msg_mod = msg; p.hb.carry_mod = carry; p.hb.grouping = grouping;
     p.lwe_std = lwe_std; p.glwe_std = glwe_std;
     return p;
 }
@@ -27,11 +27,14 @@ const Params& params_by_name(const std::string& name) {
         {"shortint_m2c1", mk("shortint_m2c1", 708, 3, 512, 18, 1, 3, 4, 64, 1, 4, 2, 1.3292631075564e-5, 3.45253423096e-13)},
         // PARAM_MESSAGE_2_CARRY_2_KS_PBS
         {"shortint_m2c2", mk("shortint_m2c2", 742, 1, 2048, 23, 1, 3, 5, 64, 1, 4, 4, 7.069849454709433e-6, 2.94036403378e-16)},
+        // PARAM_MULTI_BIT_MESSAGE_2_CARRY_2_GROUP_3_KS_PBS: the reference's arithmetic-mode set (src/bin/helm.rs:81-86)
+        {"shortint_multibit_m2c2_g3", mk("shortint_multibit_m2c2_g3", 888, 1, 2048, 21, 1, 4, 4, 64, 1, 4, 4, 6.125031601933181e-7, 2.9403601535432533e-16, 3)},
         // concrete-core GPU path of the reference (src/bin/helm.rs:141-146)
         {"concrete_gpu", mk("concrete_gpu", 512, 1, 1024, 7, 3, 2, 8, 32, 0, 0, 0, 2.9802322387695312e-8, 2.9802322387695312e-8)},
         // small sets for fast tests (NOT secure): same kernel instances as the real ones
         {"toy32", mk("toy32", 48, 2, 512, 6, 3, 3, 4, 32, 0, 0, 0, 9.5367431640625e-7, 3.725290298461914e-9)},
         {"toy64", mk("toy64", 40, 1, 2048, 23, 1, 3, 5, 64, 1, 4, 4, 5.960464477539063e-8, 2.220446049250313e-16)},
+        {"toy64m", mk("toy64m", 36, 1, 2048, 21, 1, 4, 4, 64, 1, 4, 4, 5.960464477539063e-8, 2.220446049250313e-16, 3)},
         {"toy64b", mk("toy64b", 36, 3, 512, 18, 1, 3, 4, 64, 1, 2, 2, 5.960464477539063e-8, 2.2737367544323206e-13)},
     };
     auto it = sets.find(name);
@@ -170,11 +173,21 @@ template <class T> static void gen_server_keys_t(const ClientKey& ck, const Rng&
     const Params& p = ck.p;
     const int n = p.hb.n, k = p.hb.k, N = p.hb.N, l = p.hb.pbs_level, lk = p.hb.ks_level, BITS = (int)sizeof(T) * 8;
     const size_t row_words = (size_t)(k + 1) * N;
-    sk->bsk.assign((size_t)n * l * (k + 1) * row_words * sizeof(T), 0);
+    // multi-bit (grouping g > 1): per group of g key bits 2^g GGSWs, pattern q encrypts prod_j (bit_j(q) ? s_j : 1 - s_j)
+    const int grp = p.hb.grouping > 1 ? p.hb.grouping : 1, pats = grp > 1 ? (1 << grp) : 1;
+    if (grp > 1 && n % grp) throw Error("multi-bit parameter set: n must be a multiple of the grouping factor");
+    const int n_ggsw = grp > 1 ? (n / grp) * pats : n;
+    sk->bsk.assign((size_t)n_ggsw * l * (k + 1) * row_words * sizeof(T), 0);
     T* bsk = (T*)sk->bsk.data();
     // BSK_i = GGSW(s_i): for level lev and row r, a GLWE encryption of 0 plus s_i * q/B^lev on component r (App. A.2)
 #pragma omp parallel for schedule(dynamic, 4)
-    for (int i = 0; i < n; ++i) {
+    for (int i = 0; i < n_ggsw; ++i) {
+        int message = ck.lwe_sk[grp > 1 ? 0 : i];
+        if (grp > 1) {
+            const int g0 = (i / pats) * grp, q = i % pats;
+            message = 1;
+            for (int j = 0; j < grp; ++j) message &= ((q >> j) & 1) ? ck.lwe_sk[g0 + j] : 1 - ck.lwe_sk[g0 + j];
+        }
         Rng r = base.fork(0x10000u + 2u * (uint32_t)i), rn = base.fork(0x10001u + 2u * (uint32_t)i);   // masks, noise
         for (int lev = 1; lev <= l; ++lev)
             for (int row = 0; row <= k; ++row) {
@@ -186,7 +199,7 @@ template <class T> static void gen_server_keys_t(const ClientKey& ck, const Rng&
                     for (int c = 0; c < N; ++c) a[c] = (T)r.next();
                     poly_mul_binary_acc<T>(a, ck.glwe_sk.data() + (size_t)j * N, N, body);
                 }
-                if (ck.lwe_sk[i]) g[(size_t)row * N] += ((T)1) << (BITS - p.hb.pbs_base_log * lev);
+                if (message) g[(size_t)row * N] += ((T)1) << (BITS - p.hb.pbs_base_log * lev);
             }
     }
     // KSK[i][lev] = LWE_small( s_big[i] * q / B_ks^lev )

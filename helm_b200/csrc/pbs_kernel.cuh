@@ -50,6 +50,7 @@ struct PbsArgs {
     const double2* wtab;                     // [2][M]: WA[k0*RB+j0], WB[j0*RA+k0]
     int32_t n;  int32_t base_log;
     uint16_t* atil; uint32_t atil_stride;    // pbs16_kernel: switched masks, [jobs padded to the CTA tile][atil_stride]
+    const double2* roots;                    // multi-bit instances: e^{i pi t / N}, t < 2N (spectra of the monomials X^e)
 };
 
 template <class T> struct TorusOps;
@@ -222,8 +223,15 @@ __device__ unsigned long long g_phase_clk[16];
 // STAGE (narrow-batch instances): BSK_{i+1} is copied into shared memory by one cp.async.bulk while step i runs its inverse
 // transforms and step i+1 its rotation / forward transforms, so the MAC reads the key at shared-memory speed instead of
 // waiting on L2 (with one gate per CTA nothing else amortises that latency; it was 37 % of the step, profiles/r01_v6_*).
-template <class T, int N, int K, int L, int RA, int RB, int G, int NT, int MINB, bool STAGE = false>
+// MB > 1: multi-bit blind rotation with grouping factor MB (tfhe-rs multi_bit PBS, the reference's arithmetic-mode parameter set,
+// src/bin/helm.rs:81-86).  The key holds 2^MB GGSWs per group of MB mask elements; per group, pattern q carries the monomial
+// X^{e_q}, e_q = sum of the switched mask elements selected by the bits of q, and ONE external product is made with
+// sum_q GGSW_q X^{e_q} (combined per gate in the Fourier domain, where X^e is the spectrum roots[e (4f+1) mod 2N] at frequency
+// f): acc <- ExtProd(combined, acc).  n / MB sequential steps instead of n; the digits are those of the accumulator itself (no
+// rotate-subtract) and the result replaces the accumulator.  The key slices (2^MB x 64 KB) are read through L2, once per CTA.
+template <class T, int N, int K, int L, int RA, int RB, int G, int NT, int MINB, bool STAGE = false, int MB = 0>
 __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
+    static_assert(MB == 0 || (MB >= 2 && MB <= 4 && !STAGE), "multi-bit instances read the key through L2");
     using C = PbsCfg<T, N, K, L, RA, RB, G>;
     constexpr int M = C::M, ROWS = C::ROWS, XROW = C::XROW;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -308,13 +316,14 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
     }
     __syncthreads();
 
-    // ---- n CMUX steps
+    // ---- n CMUX steps (multi-bit: n / MB external products)
     HB_PC_DECL;
-    for (int i = 0; i < n; ++i) {
+    const int n_steps = MB > 1 ? n / MB : n;
+    for (int i = 0; i < n_steps; ++i) {
         HB_PC_MARK(7);
-        int any = 0;
+        int any = MB > 1 ? 1 : 0;                     // a multi-bit step is an external product even when every exponent is 0
 #pragma unroll
-        for (int g = 0; g < G; ++g) any |= atil[g * (n + 1) + i];
+        for (int g = 0; g < G; ++g) any |= atil[g * (n + 1) + (MB > 1 ? 0 : i)];
         if (any == 0) {                               // uniform across the CTA
             if (STAGE) {                              // consume the block in flight, start the next one
                 mbar_wait(kbar, kphase); kphase ^= 1u;
@@ -331,8 +340,21 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
         // shared memory in the order the FFT pass reads them ([row][part][j0], part = a pair of j1)
         for (int t = tid; t < G * (K + 1) * PARTS * RB; t += NT) {
             const int j0 = t % RB, part = (t / RB) % PARTS, r = (t / (RB * PARTS)) % (K + 1), g = t / (RB * PARTS * (K + 1));
-            const int a = atil[g * (n + 1) + i];
+            const int a = MB > 1 ? 0 : atil[g * (n + 1) + i];
             const T* ap = acc + ((size_t)g * (K + 1) + r) * N;
+            if constexpr (MB > 1) {                   // digits of the accumulator itself
+                int32_t dgm[4][L];
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    const int c = j0 + RB * (2 * part + u);
+                    digits_all<T, L>(ap[c], A.base_log, dgm[2 * u]);
+                    digits_all<T, L>(ap[c + M], A.base_log, dgm[2 * u + 1]);
+                }
+#pragma unroll
+                for (int lev = 0; lev < L; ++lev)
+                    digs[(((size_t)g * ROWS + lev * (K + 1) + r) * PARTS + part) * RB + j0] = Dig::make(dgm[0][lev], dgm[1][lev], dgm[2][lev], dgm[3][lev]);
+                continue;
+            }
 #ifndef HB_PBS_GENERIC_DIGITS
             if constexpr (sizeof(T) == 4 && 7 * L <= 24) {
                 // u32 sets with the usual bases: all four values decomposed at once in byte lanes (digits_u32.cuh);
@@ -437,6 +459,61 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
         HB_PC_MARK(2);
         if (STAGE) { mbar_wait(kbar, kphase); kphase ^= 1u; }
         HB_PC_MARK(3);
+        if constexpr (MB > 1) {
+            // exponents of this group's patterns per gate (pattern 0 is the constant monomial)
+            int ex[G][1 << MB];
+#pragma unroll
+            for (int g = 0; g < G; ++g)
+#pragma unroll
+                for (int q = 0; q < (1 << MB); ++q) {
+                    int e = 0;
+#pragma unroll
+                    for (int j = 0; j < MB; ++j) if ((q >> j) & 1) e += atil[g * (n + 1) + i * MB + j];
+                    ex[g][q] = e & (2 * N - 1);
+                }
+            for (int pos = tid; pos < M; pos += NT) {
+                const int s = (pos / RB) * (RB + 1) + (pos % RB);
+                const int f4 = 4 * ((pos / RB) + RA * (pos % RB)) + 1;        // position k0*RB + k1 holds frequency k0 + RA*k1
+                double2 cmb[G][ROWS][K + 1];                                  // combined key entry per gate
+#pragma unroll
+                for (int g = 0; g < G; ++g)
+#pragma unroll
+                    for (int row = 0; row < ROWS; ++row)
+#pragma unroll
+                        for (int j = 0; j <= K; ++j) cmb[g][row][j] = make_double2(0.0, 0.0);
+                const double2* bp = A.bsk + (size_t)i * (1 << MB) * ROWS * (K + 1) * M + pos;
+#pragma unroll 2
+                for (int q = 0; q < (1 << MB); ++q) {
+                    double2 b[ROWS][K + 1];
+#pragma unroll
+                    for (int row = 0; row < ROWS; ++row)
+#pragma unroll
+                        for (int j = 0; j <= K; ++j) b[row][j] = __ldg(bp + ((size_t)q * ROWS * (K + 1) + row * (K + 1) + j) * M);
+#pragma unroll
+                    for (int g = 0; g < G; ++g) {
+                        const double2 m = __ldg(A.roots + ((ex[g][q] * f4) & (2 * N - 1)));
+#pragma unroll
+                        for (int row = 0; row < ROWS; ++row)
+#pragma unroll
+                            for (int j = 0; j <= K; ++j) cfma(cmb[g][row][j], b[row][j], m);
+                    }
+                }
+#pragma unroll
+                for (int g = 0; g < G; ++g) {
+                    double2 o[K + 1];
+#pragma unroll
+                    for (int j = 0; j <= K; ++j) o[j] = make_double2(0.0, 0.0);
+#pragma unroll
+                    for (int row = 0; row < ROWS; ++row) {
+                        const double2 f = X[((size_t)g * ROWS + row) * XROW + s];
+#pragma unroll
+                        for (int j = 0; j <= K; ++j) cfma(o[j], f, cmb[g][row][j]);
+                    }
+#pragma unroll
+                    for (int j = 0; j <= K; ++j) X[((size_t)g * ROWS + j) * XROW + s] = o[j];
+                }
+            }
+        } else
         for (int pos = tid; pos < M; pos += NT) {
             const int s = (pos / RB) * (RB + 1) + (pos % RB);
             double2 o[G][K + 1];
@@ -524,8 +601,8 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
 #pragma unroll
                 for (int u = 0; u < TWCH; ++u) {
                     const double2 z = cmul_tw<-1>(x[brev<RA>(c0 + u)], (c0 + u) * C::TWA);
-                    lo[u] += TorusOps<T>::round_add(z.x);
-                    hi[u] += TorusOps<T>::round_add(z.y);
+                    if (MB > 1) { lo[u] = TorusOps<T>::round_add(z.x); hi[u] = TorusOps<T>::round_add(z.y); }   // acc <- product
+                    else { lo[u] += TorusOps<T>::round_add(z.x); hi[u] += TorusOps<T>::round_add(z.y); }
                 }
 #pragma unroll
                 for (int u = 0; u < TWCH; ++u) { ap[j0 + RB * (c0 + u)] = lo[u]; ap[j0 + RB * (c0 + u) + M] = hi[u]; }
@@ -555,8 +632,8 @@ __global__ void __launch_bounds__(NT, MINB) pbs_kernel(const PbsArgs A) {
                 const int e = tid + q * NT;
                 if (e < G * (K + 1) * M) {
                     T* ap = acc + (size_t)(e / M) * N;
-                    ap[e % M] = lo[q] + TorusOps<T>::round_add(z[q].x);
-                    ap[e % M + M] = hi[q] + TorusOps<T>::round_add(z[q].y);
+                    ap[e % M] = (MB > 1 ? (T)0 : lo[q]) + TorusOps<T>::round_add(z[q].x);
+                    ap[e % M + M] = (MB > 1 ? (T)0 : hi[q]) + TorusOps<T>::round_add(z[q].y);
                 }
             }
         }
@@ -610,6 +687,15 @@ __global__ void bsk_fft_kernel(const T* __restrict__ std_bsk, double2* __restric
         dft_regs<RB, 1>(x);
 #pragma unroll
         for (int k1 = 0; k1 < RB; ++k1) out[(size_t)blockIdx.x * M + k0 * RB + k1] = x[brev<RB>(k1)];
+    }
+}
+
+// roots[t] = e^{i pi t / N}, t < 2N: the spectrum of the monomial X^e at frequency f is roots[e (4f+1) mod 2N] (multi-bit instances)
+__global__ void roots_kernel(double2* roots, int N) {
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < 2 * N; t += gridDim.x * blockDim.x) {
+        double s, c;
+        sincospi((double)t / (double)N, &s, &c);
+        roots[t] = make_double2(c, s);
     }
 }
 

@@ -20,7 +20,7 @@ OP_NAMES = {"and": AND, "nand": NAND, "or": OR, "nor": NOR, "xor": XOR, "xnor": 
 
 class HbParams(C.Structure):
     _fields_ = [(f, C.c_int32) for f in ("n", "k", "N", "pbs_base_log", "pbs_level", "ks_base_log", "ks_level",
-                                         "torus_bits", "order", "msg_mod", "carry_mod")]
+                                         "torus_bits", "order", "msg_mod", "carry_mod", "grouping")]
 
 
 class HbGate(C.Structure):
@@ -139,7 +139,7 @@ class Engine:
         if st != HB_OK:
             raise EngineError("hb_ctx_create: %s" % self.L.hb_last_error(None).decode())
         keys = [f for f, _ in HbParams._fields_]
-        self.params = {k: int(params[k]) for k in keys}
+        self.params = {k: int(params.get(k, 0)) for k in keys}
         self.P = HbParams(**self.params)
         self._ck(self.L.hb_set_params(self.h, C.byref(self.P)), "hb_set_params")
         self.dtype = np.uint32 if self.P.torus_bits == 32 else np.uint64

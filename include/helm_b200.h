@@ -45,6 +45,10 @@ typedef struct {
     int32_t order;                      /* 0 = PBS then KS (boolean; wires under the small key)
                                            1 = KS then PBS (shortint; wires under the big key) */
     int32_t msg_mod, carry_mod;         /* shortint only */
+    int32_t grouping;                   /* 0 / 1: classic blind rotation.  g > 1 (u64, k = 1, N = 2048, pbs_level = 1 instance): multi-bit
+                                           blind rotation with grouping factor g -- the reference's arithmetic-mode set
+                                           PARAM_MULTI_BIT_MESSAGE_2_CARRY_2_GROUP_3_KS_PBS (src/bin/helm.rs:81-86): n/g sequential steps, the
+                                           key holds 2^g GGSWs per group of g key bits (pattern q encrypts prod_j (bit_j(q) ? s_j : 1 - s_j)) */
 } hb_params;
 
 /* gate opcodes (GateType of src/gates.rs:23-45 that reach the FHE library) */
@@ -87,7 +91,8 @@ hb_status hb_ctx_create_multi(const int32_t* devices, int32_t n_devices, uint32_
 hb_status hb_ctx_destroy(hb_ctx*);
 const char* hb_last_error(const hb_ctx*);          /* ctx may be NULL: last creation error */
 hb_status hb_set_params(hb_ctx*, const hb_params*);
-/* standard-domain GGSW list, layout [n][level 1..l][row 0..k][poly 0..k][N]; transformed once, resident */
+/* standard-domain GGSW list, layout [n][level 1..l][row 0..k][poly 0..k][N] (multi-bit: [n/g][2^g][level][row][poly][N]);
+ * transformed once, resident */
 hb_status hb_load_bsk(hb_ctx*, const void* bsk, size_t bytes);
 /* layout [kN][level 1..l_ks][n+1]; resident */
 hb_status hb_load_ksk(hb_ctx*, const void* ksk, size_t bytes);

@@ -30,7 +30,7 @@ def test_gate_struct_layout():
     from helm_b200 import engine
     assert C.sizeof(engine.HbGate) == 32 and engine.GATE_DTYPE.itemsize == 32
     assert engine.GATE_DTYPE.fields["out"][1] == 20 and engine.GATE_DTYPE.fields["lut"][1] == 24
-    assert C.sizeof(engine.HbParams) == 44
+    assert C.sizeof(engine.HbParams) == 48
     # hb_sop { u8 kind, u8 n_in, i8 coef[4], i16 cst, u32 in[4], u32 out, u64 table }
     assert engine.SOP_DTYPE.itemsize == 40 and engine.SOP_DTYPE.fields["cst"][1] == 6
     assert engine.SOP_DTYPE.fields["out"][1] == 24 and engine.SOP_DTYPE.fields["table"][1] == 32
