@@ -12,6 +12,7 @@
 #include "../../include/helm_b200.h"
 #include "pbs_kernel.cuh"
 #include "pbs16_kernel.cuh"
+#include "pbs3_kernel.cuh"
 #ifndef HB_TMEMW
 #define HB_TMEMW true
 #endif
@@ -222,6 +223,9 @@ struct Shape {
     // between one and small2_waves x SMs x 2 bootstraps: two gates per CTA (one wave of those beats two waves of the above)
     size_t (*small2_smem)(int n) = nullptr;
     cudaError_t (*small2_launch)(const PbsArgs&, cudaStream_t, size_t smem) = nullptr;
+    // third-generation one-gate instance (pbs3_kernel.cuh); preferred over small / small2 unless HB_PBS3=0
+    size_t (*small3_smem)(int n) = nullptr;
+    cudaError_t (*small3_launch)(const PbsArgs&, cudaStream_t, size_t smem) = nullptr;
 };
 template <class Small> constexpr Shape with_small(Shape s) { s.small_smem = &Small::smem; s.small_launch = &Small::launch; return s; }
 template <class Small2> constexpr Shape with_small2(Shape s) { s.small2_smem = &Small2::smem; s.small2_launch = &Small2::launch; return s; }
@@ -254,6 +258,21 @@ struct Inst {
     static constexpr Shape shape() { Shape s{(int)sizeof(T) * 8, N, K, L, RA, RB, G, NT, &smem, &launch, &bsk_fft}; s.MB = MB; return s; }
 };
 
+// narrow batches, third generation (pbs3_kernel.cuh): one gate per CTA, three-stage transforms on M / 8 threads each
+template <class T, int N, int K, int L, int R3, int KA, int NT, bool STAGE, int MB = 0>
+struct Inst3 {
+    using C = Pbs3Cfg<T, N, K, L, 8, 8, R3, KA, NT>;
+    static size_t smem(int n) { return C::smem_bytes(n, STAGE); }
+    static cudaError_t launch(const PbsArgs& a, cudaStream_t s, size_t smem) {
+        auto kern = pbs3_kernel<T, N, K, L, 8, 8, R3, KA, NT, STAGE, MB>;
+        static SmemOptIn opt;
+        if (cudaError_t e = opt.ensure(kern, PBS_DYN_SMEM_MAX)) return e;
+        kern<<<a.n_jobs, NT, smem, s>>>(a);
+        return cudaGetLastError();
+    }
+};
+template <class Small> constexpr Shape with_small3(Shape s) { s.small3_smem = &Small::smem; s.small3_launch = &Small::launch; return s; }
+
 // N = 512 shapes run the half-warp-per-polynomial kernel (pbs16_kernel.cuh); the key transform and the Fourier key layout are shared
 template <class T, int K, int L, int BL, int G, int MINB, bool TMEMW>
 struct Inst16 {
@@ -272,22 +291,37 @@ struct Inst16 {
 
 const Shape g_shapes[] = {
     // tfhe boolean DEFAULT_PARAMETERS
-    with_small2<Inst<uint32_t, 512, 2, 3, 16, 16, 2, HB_SMALL_NT, 1, HB_STAGE_KEY>>(
-        with_small<Inst<uint32_t, 512, 2, 3, 16, 16, 1, HB_SMALL_NT, 1, HB_STAGE_KEY>>(Inst16<uint32_t, 2, 3, 6, HB_PBS16_G, 8 / HB_PBS16_G, HB_TMEMW>::shape())),
+    // pbs3 measured per shape (tests/tools/narrow_sweep.py, 100 bootstraps): boolean 2.63 vs 2.50 ms and M1C1 2.02 vs 1.97 ms (slower: on one
+    // SM the N = 512 step is bound by shared-memory bandwidth and the FP64 pipe, not by the chain length), M2C2 3.34 vs 5.00 ms, multi-bit
+    // 3.05 vs 4.27 ms (faster) => used for the N = 2048 shapes; -DHB_PBS3_ALL builds it for every shape (A/B)
+#ifdef HB_PBS3_ALL
+    with_small3<Inst3<uint32_t, 512, 2, 3, 4, 16, 384, true>>(
+#else
+    (
+#endif
+        with_small2<Inst<uint32_t, 512, 2, 3, 16, 16, 2, HB_SMALL_NT, 1, HB_STAGE_KEY>>(
+        with_small<Inst<uint32_t, 512, 2, 3, 16, 16, 1, HB_SMALL_NT, 1, HB_STAGE_KEY>>(Inst16<uint32_t, 2, 3, 6, HB_PBS16_G, 8 / HB_PBS16_G, HB_TMEMW>::shape()))),
     Inst<uint32_t, 1024, 1, 3, 16, 32, 1, 192, 2>::shape(),    // concrete-core GPU path of the reference
     // PARAM_MESSAGE_1_CARRY_1_KS_PBS / PARAM_MESSAGE_2_CARRY_1_KS_PBS
 #ifndef HB_PBS16_U64_G
 #define HB_PBS16_U64_G 2
 #endif
 #if HB_PBS16_U64_G > 0
-    with_small<Inst<uint64_t, 512, 3, 1, 16, 16, 1, 256, 1, HB_STAGE_KEY>>(Inst16<uint64_t, 3, 1, 18, HB_PBS16_U64_G, 6 / HB_PBS16_U64_G, HB_TMEMW>::shape()),
+#ifdef HB_PBS3_ALL
+    with_small3<Inst3<uint64_t, 512, 3, 1, 4, 16, 256, true>>(
+#else
+    (
+#endif
+        with_small<Inst<uint64_t, 512, 3, 1, 16, 16, 1, 256, 1, HB_STAGE_KEY>>(Inst16<uint64_t, 3, 1, 18, HB_PBS16_U64_G, 6 / HB_PBS16_U64_G, HB_TMEMW>::shape())),
 #else
     with_small<Inst<uint64_t, 512, 3, 1, 16, 16, 1, 256, 1, HB_STAGE_KEY>>(Inst<uint64_t, 512, 3, 1, 16, 16, 2, 128, 2>::shape()),
 #endif
     // PARAM_MESSAGE_2_CARRY_2_KS_PBS
-    with_small<Inst<uint64_t, 2048, 1, 1, 32, 32, 1, 256, 1, HB_STAGE_KEY>>(Inst<uint64_t, 2048, 1, 1, 32, 32, 2, 128, 1>::shape()),
+    with_small3<Inst3<uint64_t, 2048, 1, 1, 16, 32, 512, true>>(
+        with_small<Inst<uint64_t, 2048, 1, 1, 32, 32, 1, 256, 1, HB_STAGE_KEY>>(Inst<uint64_t, 2048, 1, 1, 32, 32, 2, 128, 1>::shape())),
     // PARAM_MULTI_BIT_MESSAGE_2_CARRY_2_GROUP_3_KS_PBS (the reference's arithmetic mode, src/bin/helm.rs:81-86): multi-bit, grouping 3
-    with_small<Inst<uint64_t, 2048, 1, 1, 32, 32, 1, 256, 1, false, 3>>(Inst<uint64_t, 2048, 1, 1, 32, 32, 2, 128, 1, false, 3>::shape()),
+    with_small3<Inst3<uint64_t, 2048, 1, 1, 16, 32, 512, false, 3>>(
+        with_small<Inst<uint64_t, 2048, 1, 1, 32, 32, 1, 256, 1, false, 3>>(Inst<uint64_t, 2048, 1, 1, 32, 32, 2, 128, 1, false, 3>::shape())),
 };
 
 int find_shape(const hb_params& p) {
@@ -375,6 +409,17 @@ hb_status launch_pbs(hb_ctx* c, const void* in, uint32_t in_stride, void* out, u
     static const int small_on = getenv("HB_PBS_SMALL") ? atoi(getenv("HB_PBS_SMALL")) : 1;
     static const int small_max_env = getenv("HB_PBS_SMALL_MAX") ? atoi(getenv("HB_PBS_SMALL_MAX")) : 0;
     static const int small2_max = getenv("HB_PBS_SMALL2_MAX") ? atoi(getenv("HB_PBS_SMALL2_MAX")) : 2;
+    // third-generation one-gate kernel: up to small3_max waves of one CTA per SM (HB_PBS3=0 falls back to the instances below)
+    static const int small3_on = getenv("HB_PBS3") ? atoi(getenv("HB_PBS3")) : 1;
+    static const int small3_max = getenv("HB_PBS3_MAX") ? atoi(getenv("HB_PBS3_MAX")) : 1;
+    if (small_on && small3_on && sh.small3_launch && n_jobs <= (uint32_t)(small3_max * c->sm_count)) {
+        const size_t sm = sh.small3_smem(c->p.n);
+        if (sm <= PBS_DYN_SMEM_MAX) {
+            CU(c, sh.small3_launch(a, c->stream, sm));
+            c->stats.kernel_launches++; c->stats.pbs_count += n_jobs;
+            return HB_OK;
+        }
+    }
     const bool pair_ok = small_on && sh.small2_launch && small2_max > 0;
     const int small_max = small_max_env ? small_max_env : 1;
     if (pair_ok && n_jobs > (uint32_t)(small_max * c->sm_count) && n_jobs <= (uint32_t)(small2_max * c->sm_count)) {

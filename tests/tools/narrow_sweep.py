@@ -46,6 +46,9 @@ for W in widths:
             names = ["P1a", "P1b", "P2+bar", "keywait", "P3+bar", "P4", "P5+bar", "looptop", "P1b:load+twist", "P1b:dft", "P1b:tw+store",
                      "P4:load", "P4:dft", "P4:tw+store", "P5:load", "P5:dft"]
             n = K.params["n"]
+            if os.environ.get("HB_PBS3", "1") != "0" and W <= 148:
+                names = ["P1 decompose", "F1", "F2", "F3+bar", "keywait", "MAC+bar", "I3", "I2", "I1+bar", "top", "-", "-", "-", "-", "-", "-"]
+                n = n // max(1, K.params.get("grouping", 0) or 1)
             if os.environ.get("SWEEP_PBS16"):
                 names = ["A", "B", "wait+store", "C", "load+bar", "D", "lastwait", "O+bar", "E", "F", "top", "rotate-pk", "-", "-", "-", "-"]
-            print("   cycles/step: " + "  ".join("%s %.0f" % (nm, v / n) for nm, v in zip(names, buf)) + "  total %.0f" % (sum(buf[:8]) / n))
+            print("   cycles/step: " + "  ".join("%s %.0f" % (nm, v / n) for nm, v in zip(names, buf)) + "  total %.0f" % (sum(buf[:10 if os.environ.get("HB_PBS3", "1") != "0" and W <= 148 else 8]) / n))
