@@ -13,6 +13,7 @@
 #include "pbs_kernel.cuh"
 #include "pbs16_kernel.cuh"
 #include "pbs3_kernel.cuh"
+#include "pbs3c_kernel.cuh"
 #ifndef HB_TMEMW
 #define HB_TMEMW true
 #endif
@@ -96,6 +97,7 @@ struct hb_ctx {
     hb_stats_t stats{};
     std::string err;
     int sm_count = 0;
+    int cluster_cap = -1;                  // resident clusters of the cluster-split kernel on this device (-1: not asked yet)
     // multi-device group (hb_ctx_create_multi): the group context owns one ordinary context per device and fans every call
     // out; `level_ev` of a member = "my share of the current level is evaluated and pushed to every peer"
     std::vector<hb_ctx*> subs;
@@ -226,6 +228,10 @@ struct Shape {
     // third-generation one-gate instance (pbs3_kernel.cuh); preferred over small / small2 unless HB_PBS3=0
     size_t (*small3_smem)(int n) = nullptr;
     cudaError_t (*small3_launch)(const PbsArgs&, cudaStream_t, size_t smem) = nullptr;
+    // one bootstrap per cluster of K+1 CTAs (pbs3c_kernel.cuh): batches of at most cluster_max() bootstraps
+    size_t (*cluster_smem)(int n) = nullptr;
+    cudaError_t (*cluster_launch)(const PbsArgs&, cudaStream_t, size_t smem) = nullptr;
+    int (*cluster_max)(size_t smem) = nullptr;
 };
 template <class Small> constexpr Shape with_small(Shape s) { s.small_smem = &Small::smem; s.small_launch = &Small::launch; return s; }
 template <class Small2> constexpr Shape with_small2(Shape s) { s.small2_smem = &Small2::smem; s.small2_launch = &Small2::launch; return s; }
@@ -271,6 +277,35 @@ struct Inst3 {
         return cudaGetLastError();
     }
 };
+// narrowest batches: one bootstrap per cluster of K+1 CTAs (pbs3c_kernel.cuh).  The request is padded beyond half an SM's shared
+// memory so that the CTAs of a cluster sit on different SMs (the point of the split).
+template <class T, int N, int K, int L, int R3, int KA, int NT>
+struct Inst3c {
+    using C = Pbs3cCfg<T, N, K, L, R3, KA, NT>;
+    static size_t smem(int n) { const size_t b = C::smem_bytes(n); return b < 116 * 1024 ? 116 * 1024 : b; }
+    static cudaError_t launch(const PbsArgs& a, cudaStream_t s, size_t smem) {
+        auto kern = pbs3c_kernel<T, N, K, L, R3, KA, NT>;
+        static SmemOptIn opt;
+        if (cudaError_t e = opt.ensure(kern, PBS_DYN_SMEM_MAX)) return e;
+        kern<<<a.n_jobs * (K + 1), NT, smem, s>>>(a);
+        return cudaGetLastError();
+    }
+    // clusters of this kernel that can be resident at once on the current device (0 on error)
+    static int max_clusters(size_t smem) {
+        auto kern = pbs3c_kernel<T, N, K, L, R3, KA, NT>;
+        static SmemOptIn opt;
+        if (opt.ensure(kern, PBS_DYN_SMEM_MAX) != cudaSuccess) return 0;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((K + 1) * 64); cfg.blockDim = dim3(NT); cfg.dynamicSmemBytes = smem;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = K + 1; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        int nc = 0;
+        if (cudaOccupancyMaxActiveClusters(&nc, kern, &cfg) != cudaSuccess) { (void)cudaGetLastError(); return 0; }
+        return nc;
+    }
+};
+template <class Cl> constexpr Shape with_cluster(Shape s) { s.cluster_smem = &Cl::smem; s.cluster_launch = &Cl::launch; s.cluster_max = &Cl::max_clusters; return s; }
 template <class Small> constexpr Shape with_small3(Shape s) { s.small3_smem = &Small::smem; s.small3_launch = &Small::launch; return s; }
 
 // N = 512 shapes run the half-warp-per-polynomial kernel (pbs16_kernel.cuh); the key transform and the Fourier key layout are shared
@@ -294,13 +329,14 @@ const Shape g_shapes[] = {
     // pbs3 measured per shape (tests/tools/narrow_sweep.py, 100 bootstraps): boolean 2.63 vs 2.50 ms and M1C1 2.02 vs 1.97 ms (slower: on one
     // SM the N = 512 step is bound by shared-memory bandwidth and the FP64 pipe, not by the chain length), M2C2 3.34 vs 5.00 ms, multi-bit
     // 3.05 vs 4.27 ms (faster) => used for the N = 2048 shapes; -DHB_PBS3_ALL builds it for every shape (A/B)
+    with_cluster<Inst3c<uint32_t, 512, 2, 3, 4, 16, 128>>(
 #ifdef HB_PBS3_ALL
     with_small3<Inst3<uint32_t, 512, 2, 3, 4, 16, 384, true>>(
 #else
     (
 #endif
         with_small2<Inst<uint32_t, 512, 2, 3, 16, 16, 2, HB_SMALL_NT, 1, HB_STAGE_KEY>>(
-        with_small<Inst<uint32_t, 512, 2, 3, 16, 16, 1, HB_SMALL_NT, 1, HB_STAGE_KEY>>(Inst16<uint32_t, 2, 3, 6, HB_PBS16_G, 8 / HB_PBS16_G, HB_TMEMW>::shape()))),
+        with_small<Inst<uint32_t, 512, 2, 3, 16, 16, 1, HB_SMALL_NT, 1, HB_STAGE_KEY>>(Inst16<uint32_t, 2, 3, 6, HB_PBS16_G, 8 / HB_PBS16_G, HB_TMEMW>::shape())))),
     Inst<uint32_t, 1024, 1, 3, 16, 32, 1, 192, 2>::shape(),    // concrete-core GPU path of the reference
     // PARAM_MESSAGE_1_CARRY_1_KS_PBS / PARAM_MESSAGE_2_CARRY_1_KS_PBS
 #ifndef HB_PBS16_U64_G
@@ -409,6 +445,17 @@ hb_status launch_pbs(hb_ctx* c, const void* in, uint32_t in_stride, void* out, u
     static const int small_on = getenv("HB_PBS_SMALL") ? atoi(getenv("HB_PBS_SMALL")) : 1;
     static const int small_max_env = getenv("HB_PBS_SMALL_MAX") ? atoi(getenv("HB_PBS_SMALL_MAX")) : 0;
     static const int small2_max = getenv("HB_PBS_SMALL2_MAX") ? atoi(getenv("HB_PBS_SMALL2_MAX")) : 2;
+    // the narrowest batches: one bootstrap per cluster of K+1 SMs (HB_PBS3C=0 disables)
+    static const int cluster_on = getenv("HB_PBS3C") ? atoi(getenv("HB_PBS3C")) : 1;
+    if (small_on && cluster_on && sh.cluster_launch) {
+        const size_t sm = sh.cluster_smem(c->p.n);
+        if (c->cluster_cap < 0) c->cluster_cap = sm <= PBS_DYN_SMEM_MAX ? sh.cluster_max(sm) : 0;
+        if (n_jobs <= (uint32_t)c->cluster_cap) {
+            CU(c, sh.cluster_launch(a, c->stream, sm));
+            c->stats.kernel_launches++; c->stats.pbs_count += n_jobs;
+            return HB_OK;
+        }
+    }
     // third-generation one-gate kernel: up to small3_max waves of one CTA per SM (HB_PBS3=0 falls back to the instances below)
     static const int small3_on = getenv("HB_PBS3") ? atoi(getenv("HB_PBS3")) : 1;
     static const int small3_max = getenv("HB_PBS3_MAX") ? atoi(getenv("HB_PBS3_MAX")) : 1;
@@ -662,7 +709,7 @@ hb_status hb_set_params(hb_ctx* c, const hb_params* p) {
     if (p->torus_bits == 32 && p->pbs_base_log > 7) return fail(c, HB_ERR_UNSUPPORTED, "u32 torus: pbs_base_log must be <= 7 (digits are staged as bytes)");
     if (p->order == 1 && (p->msg_mod * p->carry_mod < 2 || p->msg_mod * p->carry_mod > 16)) return fail(c, HB_ERR_ARG, "msg_mod*carry_mod must be in [2,16]");
     CU(c, cudaSetDevice(c->device));
-    c->p = *p; c->shape = sh; c->have_params = true; c->have_bsk = c->have_ksk = false;
+    c->p = *p; c->shape = sh; c->have_params = true; c->have_bsk = c->have_ksk = false; c->cluster_cap = -1;
     const Shape& s = g_shapes[sh];
     const int M = s.RA * s.RB;
     CU(c, c->wtab.ensure((2 * (size_t)M + 2 * (size_t)p->N) * sizeof(double2)));
