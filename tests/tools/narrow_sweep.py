@@ -49,6 +49,8 @@ for W in widths:
             if os.environ.get("HB_PBS3", "1") != "0" and W <= 148:
                 names = ["P1 decompose", "F1", "F2", "F3+bar", "keywait", "MAC+bar", "I3", "I2", "I1+bar", "top", "-", "-", "-", "-", "-", "-"]
                 n = n // max(1, K.params.get("grouping", 0) or 1)
+            if os.environ.get("SWEEP_PBS3C"):
+                names = ["P1", "F1-F3+bar", "keywait", "MAC+send+bar", "recv wait", "I3-I1+bar", "-", "-", "-", "top", "-", "-", "-", "-", "-", "-"]
             if os.environ.get("SWEEP_PBS16"):
                 names = ["A", "B", "wait+store", "C", "load+bar", "D", "lastwait", "O+bar", "E", "F", "top", "rotate-pk", "-", "-", "-", "-"]
             print("   cycles/step: " + "  ".join("%s %.0f" % (nm, v / n) for nm, v in zip(names, buf)) + "  total %.0f" % (sum(buf[:10 if os.environ.get("HB_PBS3", "1") != "0" and W <= 148 else 8]) / n))
