@@ -232,6 +232,8 @@ struct Shape {
     size_t (*cluster_smem)(int n) = nullptr;
     cudaError_t (*cluster_launch)(const PbsArgs&, cudaStream_t, size_t smem) = nullptr;
     int (*cluster_max)(size_t smem) = nullptr;
+    size_t (*wide3_smem)(int n) = nullptr;
+    cudaError_t (*wide3_launch)(const PbsArgs&, cudaStream_t, size_t smem) = nullptr;
 };
 template <class Small> constexpr Shape with_small(Shape s) { s.small_smem = &Small::smem; s.small_launch = &Small::launch; return s; }
 template <class Small2> constexpr Shape with_small2(Shape s) { s.small2_smem = &Small2::smem; s.small2_launch = &Small2::launch; return s; }
@@ -265,18 +267,20 @@ struct Inst {
 };
 
 // narrow batches, third generation (pbs3_kernel.cuh): one gate per CTA, three-stage transforms on M / 8 threads each
-template <class T, int N, int K, int L, int R3, int KA, int NT, bool STAGE, int MB = 0>
+template <class T, int N, int K, int L, int R3, int KA, int NT, bool STAGE, int MB = 0, int G = 1>
 struct Inst3 {
-    using C = Pbs3Cfg<T, N, K, L, 8, 8, R3, KA, NT>;
+    using C = Pbs3Cfg<T, N, K, L, 8, 8, R3, KA, NT, G>;
     static size_t smem(int n) { return C::smem_bytes(n, STAGE); }
     static cudaError_t launch(const PbsArgs& a, cudaStream_t s, size_t smem) {
-        auto kern = pbs3_kernel<T, N, K, L, 8, 8, R3, KA, NT, STAGE, MB>;
+        auto kern = pbs3_kernel<T, N, K, L, 8, 8, R3, KA, NT, STAGE, MB, G>;
         static SmemOptIn opt;
         if (cudaError_t e = opt.ensure(kern, PBS_DYN_SMEM_MAX)) return e;
-        kern<<<a.n_jobs, NT, smem, s>>>(a);
+        kern<<<(a.n_jobs + G - 1) / G, NT, smem, s>>>(a);
         return cudaGetLastError();
     }
 };
+// wide batches on the three-stage kernel with several gates per CTA (replaces the shape's first-generation wide instance unless HB_PBS3_WIDE=0)
+template <class Wide> constexpr Shape with_wide3(Shape s) { s.wide3_smem = &Wide::smem; s.wide3_launch = &Wide::launch; return s; }
 // narrowest batches: one bootstrap per cluster of K+1 CTAs (pbs3c_kernel.cuh).  The request is padded beyond half an SM's shared
 // memory so that the CTAs of a cluster sit on different SMs (the point of the split).
 template <class T, int N, int K, int L, int R3, int KA, int NT>
@@ -353,8 +357,8 @@ const Shape g_shapes[] = {
     with_small<Inst<uint64_t, 512, 3, 1, 16, 16, 1, 256, 1, HB_STAGE_KEY>>(Inst<uint64_t, 512, 3, 1, 16, 16, 2, 128, 2>::shape()),
 #endif
     // PARAM_MESSAGE_2_CARRY_2_KS_PBS
-    with_small3<Inst3<uint64_t, 2048, 1, 1, 16, 32, 512, true>>(
-        with_small<Inst<uint64_t, 2048, 1, 1, 32, 32, 1, 256, 1, HB_STAGE_KEY>>(Inst<uint64_t, 2048, 1, 1, 32, 32, 2, 128, 1>::shape())),
+    with_wide3<Inst3<uint64_t, 2048, 1, 1, 16, 32, 512, false, 0, 2>>(with_small3<Inst3<uint64_t, 2048, 1, 1, 16, 32, 512, true>>(
+        with_small<Inst<uint64_t, 2048, 1, 1, 32, 32, 1, 256, 1, HB_STAGE_KEY>>(Inst<uint64_t, 2048, 1, 1, 32, 32, 2, 128, 1>::shape()))),
     // PARAM_MULTI_BIT_MESSAGE_2_CARRY_2_GROUP_3_KS_PBS (the reference's arithmetic mode, src/bin/helm.rs:81-86): multi-bit, grouping 3
     with_small3<Inst3<uint64_t, 2048, 1, 1, 16, 32, 512, false, 3>>(
         with_small<Inst<uint64_t, 2048, 1, 1, 32, 32, 1, 256, 1, false, 3>>(Inst<uint64_t, 2048, 1, 1, 32, 32, 2, 128, 1, false, 3>::shape())),
@@ -458,8 +462,11 @@ hb_status launch_pbs(hb_ctx* c, const void* in, uint32_t in_stride, void* out, u
     }
     // third-generation one-gate kernel: up to small3_max waves of one CTA per SM (HB_PBS3=0 falls back to the instances below)
     static const int small3_on = getenv("HB_PBS3") ? atoi(getenv("HB_PBS3")) : 1;
-    static const int small3_max = getenv("HB_PBS3_MAX") ? atoi(getenv("HB_PBS3_MAX")) : 1;
-    if (small_on && small3_on && sh.small3_launch && n_jobs <= (uint32_t)(small3_max * c->sm_count)) {
+    // waves of it that still beat the shape's wide kernel (narrow_sweep, M2C2: a wave of 148 takes 3.34 ms, the two-gate wide instance
+    // 6.57 ms per 296 => one-gate waves win up to the point where the wide kernel's better tail packing matters; multi-bit: always)
+    static const int small3_env = getenv("HB_PBS3_MAX") ? atoi(getenv("HB_PBS3_MAX")) : 0;
+    const int small3_max = small3_env ? small3_env : sh.MB ? (1 << 20) : sh.wide3_launch ? 8 : 1;
+    if (small_on && small3_on && sh.small3_launch && n_jobs <= (uint32_t)small3_max * (uint32_t)c->sm_count) {
         const size_t sm = sh.small3_smem(c->p.n);
         if (sm <= PBS_DYN_SMEM_MAX) {
             CU(c, sh.small3_launch(a, c->stream, sm));
@@ -481,6 +488,15 @@ hb_status launch_pbs(hb_ctx* c, const void* in, uint32_t in_stride, void* out, u
         const size_t sm = sh.small_smem(c->p.n);
         if (sm <= PBS_DYN_SMEM_MAX) {
             CU(c, sh.small_launch(a, c->stream, sm));
+            c->stats.kernel_launches++; c->stats.pbs_count += n_jobs;
+            return HB_OK;
+        }
+    }
+    static const int wide3_on = getenv("HB_PBS3_WIDE") ? atoi(getenv("HB_PBS3_WIDE")) : 1;
+    if (wide3_on && sh.wide3_launch) {
+        const size_t sm = sh.wide3_smem(c->p.n);
+        if (sm <= PBS_DYN_SMEM_MAX) {
+            CU(c, sh.wide3_launch(a, c->stream, sm));
             c->stats.kernel_launches++; c->stats.pbs_count += n_jobs;
             return HB_OK;
         }

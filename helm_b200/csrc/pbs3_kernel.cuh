@@ -24,7 +24,7 @@
 
 namespace hb {
 
-template <class T, int N, int K, int L, int R1, int R2, int R3, int KA, int NT>
+template <class T, int N, int K, int L, int R1, int R2, int R3, int KA, int NT, int G = 1>
 struct Pbs3Cfg {
     static constexpr bool SMALLDIG = sizeof(T) == 4;
     using Dig = DigPack<SMALLDIG>;
@@ -35,12 +35,14 @@ struct Pbs3Cfg {
     static constexpr int XSZ = R1 * A1;                                 // double2 per transform buffer
     static constexpr int TWA = HB_TW_DEN / (4 * R1);                    // omega^{RB j1} = e^{2 pi i j1 TWA / 256}
     static_assert(R1 * R2 * R3 == M && R1 == 8 && R2 == 8, "stages 1 and 2 are radix 8: M / 8 threads per transform");
-    static_assert(A1 >= R2 * A2 && ROWS * TPT <= NT && NT % 32 == 0, "thread / buffer geometry");
+    static constexpr int NTG = NT / G;                                  // threads of one gate
+    static_assert(A1 >= R2 * A2 && ROWS * TPT <= NTG && NT % (32 * G) == 0, "thread / buffer geometry");
     static_assert(TPT % 32 == 0, "whole warps per transform");
     static constexpr size_t KEY_BYTES = (size_t)ROWS * (K + 1) * M * sizeof(double2);
     __host__ __device__ static constexpr size_t smem_core(int n) {
-        return (size_t)ROWS * XSZ * sizeof(double2) + 2 * (size_t)XSZ * sizeof(double2) + (size_t)(K + 1) * N * sizeof(T) +
-               (size_t)ROWS * PARTS * RB * sizeof(typename Dig::type) + (((size_t)(n + 1) * 2 + 15) & ~(size_t)15);
+        return 2 * (size_t)XSZ * sizeof(double2) +
+               G * ((size_t)ROWS * XSZ * sizeof(double2) + (size_t)(K + 1) * N * sizeof(T) +
+                    (size_t)ROWS * PARTS * RB * sizeof(typename Dig::type) + (((size_t)(n + 1) * 2 + 15) & ~(size_t)15));
     }
     __host__ __device__ static constexpr size_t smem_bytes(int n, bool stage) { return smem_core(n) + (stage ? KEY_BYTES + 16 : 0); }
     __host__ __device__ static constexpr int addr(int d1, int d2, int d3) { return d1 * A1 + d2 * A2 + d3; }
@@ -48,21 +50,31 @@ struct Pbs3Cfg {
 
 // STAGE: BSK_{i+1} staged in shared memory by one cp.async.bulk while step i finishes (as in pbs_kernel).  MB > 1: multi-bit blind
 // rotation with grouping factor MB (see pbs_kernel.cuh): key read through L2, combined per step with the monomial spectra.
-template <class T, int N, int K, int L, int R1, int R2, int R3, int KA, int NT, bool STAGE, int MB = 0>
+// G > 1 (wide batches of the N = 2048 shapes): G gates per CTA, NT / G threads each, in lock step; the MAC reads every key word once
+// for all G gates (no staging: the key streams through L2 once per CTA and step).
+template <class T, int N, int K, int L, int R1, int R2, int R3, int KA, int NT, bool STAGE, int MB = 0, int G = 1>
 __global__ void __launch_bounds__(NT, 1) pbs3_kernel(const PbsArgs A) {
-    using C = Pbs3Cfg<T, N, K, L, R1, R2, R3, KA, NT>;
+    using C = Pbs3Cfg<T, N, K, L, R1, R2, R3, KA, NT, G>;
+    static_assert(G == 1 || (!STAGE && MB == 0), "several gates per CTA: key through L2, classic blind rotation");
+    constexpr int NTG = C::NTG;
     using Dig = typename C::Dig;
     using DigT = typename Dig::type;
     constexpr int M = C::M, ROWS = C::ROWS, RB = C::RB, PARTS = C::PARTS, TPT = C::TPT, XSZ = C::XSZ, A1 = C::A1, A2 = C::A2, KB2 = C::KB2;
     static_assert(MB == 0 || (MB >= 2 && MB <= 4 && !STAGE), "multi-bit instances read the key through L2");
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    double2* X = reinterpret_cast<double2*>(smem_raw);                  // [ROWS][XSZ]
-    double2* TW2 = X + (size_t)ROWS * XSZ;                              // [XSZ] at addr(k1, j2, j3)
-    double2* TW3 = TW2 + XSZ;                                           // [XSZ] at addr(k1, k2, j3)
-    T* acc = reinterpret_cast<T*>(TW3 + XSZ);                           // [K+1][N]
-    DigT* digs = reinterpret_cast<DigT*>(acc + (size_t)(K + 1) * N);    // [ROWS][PARTS][RB]
-    uint16_t* atil = reinterpret_cast<uint16_t*>(digs + (size_t)ROWS * PARTS * RB);   // [n+1]
     const int tid = threadIdx.x, n = A.n;
+    const int gg = tid / NTG, gt = tid % NTG;                           // gate of this thread, thread within the gate
+    const size_t atil_pad = (((size_t)(n + 1) * 2 + 15) & ~(size_t)15) / 2;          // uint16 per gate
+    double2* TW2 = reinterpret_cast<double2*>(smem_raw);                // [XSZ] at addr(k1, j2, j3)
+    double2* TW3 = TW2 + XSZ;                                           // [XSZ] at addr(k1, k2, j3)
+    double2* Xall = TW3 + XSZ;                                          // [G][ROWS][XSZ]
+    T* accall = reinterpret_cast<T*>(Xall + (size_t)G * ROWS * XSZ);    // [G][K+1][N]
+    DigT* digsall = reinterpret_cast<DigT*>(accall + (size_t)G * (K + 1) * N);       // [G][ROWS][PARTS][RB]
+    uint16_t* atilall = reinterpret_cast<uint16_t*>(digsall + (size_t)G * ROWS * PARTS * RB);   // [G][atil_pad]
+    double2* X = Xall + (size_t)gg * ROWS * XSZ;
+    T* acc = accall + (size_t)gg * (K + 1) * N;
+    DigT* digs = digsall + (size_t)gg * ROWS * PARTS * RB;
+    uint16_t* atil = atilall + (size_t)gg * atil_pad;
     double2* KBUF = reinterpret_cast<double2*>(smem_raw + C::smem_core(n));
     const uint32_t kb_addr = (uint32_t)__cvta_generic_to_shared(KBUF);
     const uint32_t kbar = kb_addr + (uint32_t)C::KEY_BYTES;
@@ -73,9 +85,11 @@ __global__ void __launch_bounds__(NT, 1) pbs3_kernel(const PbsArgs A) {
         mbar_expect_tx(kbar, (uint32_t)C::KEY_BYTES);
         bulk_g2s(kb_addr, A.bsk, (uint32_t)C::KEY_BYTES, kbar);
     }
-    const int jid = blockIdx.x;                                         // one gate per CTA
+    const int jid = blockIdx.x * G + gg;
+    const bool live = jid < (int)A.n_jobs;                              // the last CTA of a G > 1 launch may hold padding gates
     const T* in = reinterpret_cast<const T*>(A.in);
-    const PbsJob jb = A.jobs[jid];
+    PbsJob jb = {};
+    if (live) jb = A.jobs[jid];
 
     // inter-stage twiddles from the table of 4M-th roots of unity (roots[t] = e^{2 pi i t / 4M}, 4M = 2N)
     for (int e = tid; e < M; e += NT) {
@@ -87,7 +101,7 @@ __global__ void __launch_bounds__(NT, 1) pbs3_kernel(const PbsArgs A) {
     {
         const T* s0 = in + (size_t)jb.src0 * A.in_stride;
         const T* s1 = in + (size_t)jb.src1 * A.in_stride;
-        for (int x = tid; x <= n; x += NT) {
+        for (int x = gt; x <= n; x += NTG) {
             T v = 0;
             if (jb.c0) v += (T)(int64_t)jb.c0 * s0[x];
             if (jb.c1) v += (T)(int64_t)jb.c1 * s1[x];
@@ -100,16 +114,16 @@ __global__ void __launch_bounds__(NT, 1) pbs3_kernel(const PbsArgs A) {
     // ---- accumulator = TV * X^{-b~}
     {
         const int a0 = (2 * N - atil[n]) & (2 * N - 1);
-        for (int x = tid; x < K * N; x += NT) acc[x] = 0;
-        for (int c = tid; c < N; c += NT) {
+        for (int x = gt; x < K * N; x += NTG) acc[x] = 0;
+        for (int c = gt; c < N; c += NTG) {
             int t = c - a0; if (t < 0) t += 2 * N;
-            acc[K * N + c] = t < N ? tv_body<T>(jb, N, t) : (T)(0 - tv_body<T>(jb, N, t - N));
+            acc[K * N + c] = !live ? (T)0 : t < N ? tv_body<T>(jb, N, t) : (T)(0 - tv_body<T>(jb, N, t - N));
         }
     }
     __syncthreads();
 
     // roles in the transforms: transform `tr` (forward: row of the decomposition; inverse: output polynomial), lane `lt` in it
-    const int tr = tid / TPT, lt = tid % TPT;
+    const int tr = gt / TPT, lt = gt % TPT;
     auto tsync = [&]() { if (TPT <= 32) __syncwarp(); else __syncthreads(); };
 
     const int n_steps = MB > 1 ? n / MB : n;
@@ -117,7 +131,10 @@ __global__ void __launch_bounds__(NT, 1) pbs3_kernel(const PbsArgs A) {
     for (int i = 0; i < n_steps; ++i) {
         HB_PC_MARK(9);
         const int a = MB > 1 ? 0 : atil[i];
-        if (MB == 0 && a == 0) {                      // uniform across the CTA: acc X^0 - acc = 0
+        int any = a;
+#pragma unroll
+        for (int g2 = 0; g2 < G; ++g2) any |= atilall[(size_t)g2 * atil_pad + i];
+        if (MB == 0 && any == 0) {                    // uniform across the CTA: acc X^0 - acc = 0 for every gate
             if (STAGE) {                              // consume the block in flight, start the next one
                 mbar_wait(kbar, kphase); kphase ^= 1u;
                 __syncthreads();
@@ -130,7 +147,7 @@ __global__ void __launch_bounds__(NT, 1) pbs3_kernel(const PbsArgs A) {
         }
         // ---- P1: rotate-subtract (multi-bit: the accumulator itself) and signed decomposition, once per coefficient for all L
         // levels; digits staged in the order stage 1 reads them: [row][part][j0], coefficient c = j0 + RB (2 part + u) (and c + M)
-        for (int t = tid; t < (K + 1) * PARTS * RB; t += NT) {
+        for (int t = gt; t < (K + 1) * PARTS * RB; t += NTG) {
             const int j0 = t % RB, part = (t / RB) % PARTS, r = t / (RB * PARTS);
             const T* ap = acc + (size_t)r * N;
             T v[4];
@@ -255,7 +272,7 @@ __global__ void __launch_bounds__(NT, 1) pbs3_kernel(const PbsArgs A) {
 #pragma unroll
                 for (int j = 0; j <= K; ++j) X[(size_t)j * XSZ + xa] = o[j];
             }
-        } else {
+        } else if constexpr (G == 1) {
             for (int pos = tid; pos < M; pos += NT) {
                 const int f = (pos / KB2) + KA * (pos % KB2);
                 const int xa = C::addr(f % R1, (f / R1) % R2, f / (R1 * R2));
@@ -272,6 +289,33 @@ __global__ void __launch_bounds__(NT, 1) pbs3_kernel(const PbsArgs A) {
                 }
 #pragma unroll
                 for (int j = 0; j <= K; ++j) X[(size_t)j * XSZ + xa] = o[j];
+            }
+        } else {
+            // every thread of the CTA takes positions; one read of BSK_i (registers) feeds all G gates
+            for (int pos = tid; pos < M; pos += NT) {
+                const int f = (pos / KB2) + KA * (pos % KB2);
+                const int xa = C::addr(f % R1, (f / R1) % R2, f / (R1 * R2));
+                const double2* bp = A.bsk + (size_t)i * ROWS * (K + 1) * M + pos;
+                double2 b[ROWS][K + 1];
+#pragma unroll
+                for (int row = 0; row < ROWS; ++row)
+#pragma unroll
+                    for (int j = 0; j <= K; ++j) b[row][j] = __ldg(bp + (size_t)(row * (K + 1) + j) * M);
+#pragma unroll
+                for (int g2 = 0; g2 < G; ++g2) {
+                    double2* xg = Xall + (size_t)g2 * ROWS * XSZ;
+                    double2 o[K + 1];
+#pragma unroll
+                    for (int j = 0; j <= K; ++j) o[j] = make_double2(0.0, 0.0);
+#pragma unroll
+                    for (int row = 0; row < ROWS; ++row) {
+                        const double2 fx = xg[(size_t)row * XSZ + xa];
+#pragma unroll
+                        for (int j = 0; j <= K; ++j) cfma(o[j], fx, b[row][j]);
+                    }
+#pragma unroll
+                    for (int j = 0; j <= K; ++j) xg[(size_t)j * XSZ + xa] = o[j];
+                }
             }
         }
         __syncthreads();
@@ -337,12 +381,14 @@ __global__ void __launch_bounds__(NT, 1) pbs3_kernel(const PbsArgs A) {
     HB_PC_FLUSH();
 
     // ---- epilogue: sample extract coefficient 0 (App. A.5)
-    T* o = reinterpret_cast<T*>(A.out) + (size_t)jb.dst * A.out_stride;
-    for (int x = tid; x < K * N; x += NT) {
-        const int j = x / N, c = x % N;
-        o[x] = c == 0 ? acc[j * N] : (T)(0 - acc[j * N + N - c]);
+    if (live) {
+        T* o = reinterpret_cast<T*>(A.out) + (size_t)jb.dst * A.out_stride;
+        for (int x = gt; x < K * N; x += NTG) {
+            const int j = x / N, c = x % N;
+            o[x] = c == 0 ? acc[j * N] : (T)(0 - acc[j * N + N - c]);
+        }
+        if (gt == 0) o[K * N] = acc[K * N];
     }
-    if (tid == 0) o[K * N] = acc[K * N];
 }
 
 }  // namespace hb
