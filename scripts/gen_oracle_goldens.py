@@ -48,8 +48,11 @@ def shortint_set(name, n_luts):
     table = [(3 * i + 1) % K.P.msg_mod for i in range(mc)]
     cts = np.stack([K.enc_shortint(int(v), 9000 + i) for i, v in enumerate(vals)])
     outs = np.stack([K.shortint_lut(cts[i], table, mode=O.FFT) for i in range(n_luts)])
+    extra = {}
+    if K.P.grouping > 1:                              # exact-integer outputs as well: the two back-ends must stay within the output noise
+        extra["lut_outputs_exact"] = np.stack([K.shortint_lut(cts[i], table, mode=O.EXACT) for i in range(n_luts)])
     np.savez_compressed(os.path.join(OUT, name + ".npz"), key_seed=KEY_SEED, values=vals, table=np.array(table), inputs=cts,
-                        lut_outputs_fft=outs, keyswitch=np.stack([K.keyswitch(c) for c in cts]))
+                        lut_outputs_fft=outs, keyswitch=np.stack([K.keyswitch(c) for c in cts]), **extra)
 
 
 def decomposition():
@@ -73,5 +76,6 @@ if __name__ == "__main__":
     boolean_set("boolean_default", 7)
     shortint_set("toy64b", 6)
     shortint_set("toy64", 4)
+    shortint_set("toy64m", 4)                         # multi-bit (grouping 3) blind rotation, oracle/tfhe_oracle.cpp::multibit_step_t
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))

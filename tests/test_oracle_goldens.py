@@ -49,7 +49,7 @@ def test_oracle_reproduces_boolean_goldens(name, keys_factory, oracle_mod):
         assert np.array_equal(K.pbs(lin, K.bool_tv(), mode=oracle_mod.FFT), z["pbs"])     # f64 FFT is exact on the u32 torus
 
 
-@pytest.mark.parametrize("name", ["toy64b", "toy64"])
+@pytest.mark.parametrize("name", ["toy64b", "toy64", "toy64m"])
 def test_oracle_reproduces_shortint_goldens(name, keys_factory, oracle_mod):
     z = _load(name)
     K = keys_factory(name, int(z["key_seed"]))
@@ -58,6 +58,13 @@ def test_oracle_reproduces_shortint_goldens(name, keys_factory, oracle_mod):
         assert np.array_equal(K.keyswitch(z["inputs"][i]), z["keyswitch"][i])
         out = K.shortint_lut(z["inputs"][i], table, mode=oracle_mod.FFT)
         assert K.dec_shortint(out) == table[int(z["values"][i])] == K.dec_shortint(z["lut_outputs_fft"][i])
+    if "lut_outputs_exact" in z:        # multi-bit blind rotation: the exact-integer back-end is deterministic word for word, and the
+        ex = K.shortint_lut(z["inputs"][0], table, mode=oracle_mod.EXACT)          # f64-FFT back-end stays inside the output noise of it
+        assert np.array_equal(ex, z["lut_outputs_exact"][0])
+        for i in range(len(z["inputs"])):
+            d = (int(K.phase(z["lut_outputs_exact"][i], 1)) - int(K.phase(z["lut_outputs_fft"][i], 1))) % (1 << 64)
+            assert min(d, (1 << 64) - d) < K.delta() // 64
+            assert K.dec_shortint(z["lut_outputs_exact"][i]) == table[int(z["values"][i])]
 
 
 @pytest.mark.gpu
@@ -84,7 +91,7 @@ def test_engine_reproduces_boolean_goldens(name, engine_factory):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name", ["toy64b", "toy64"])
+@pytest.mark.parametrize("name", ["toy64b", "toy64", "toy64m"])
 def test_engine_reproduces_shortint_goldens(name, keys_factory, engine_factory):
     from helm_b200 import engine as E
     z = _load(name)
