@@ -507,27 +507,46 @@ def main():
         hin_np = hin.numpy().view(eng.dtype); hout_np = hout.numpy().view(eng.dtype)
         hin_np[:] = ct0[g0:g0 + Wr]
 
+        hout2 = [hout_np, np.empty_like(hout_np)] if group else None
+        if not group:
+            hb2 = torch.empty((Wr, words), dtype=torch.int32).pin_memory()
+            hout2 = [hout_np, hb2.numpy().view(eng.dtype)]
+
+        def e2e_level(s):
+            # inputs in an even block, outputs in the odd block after it: consecutive steps touch disjoint rows, so the upload of step
+            # s+1 and the download of step s-1 (copy stream) may overlap the evaluation of step s (compute stream)
+            return 2 * (s % (DEPTH // 2)) + 1
+
         def step_e2e(s):
-            lvl = s % DEPTH + 1
-            wires.write_rows((lvl - 1) * W + g0, hin_np)       # H2D: this rank's share of the level's input wires
+            lvl = e2e_level(s)
+            if group:                                          # one process, several devices: synchronous row IO
+                wires.write_rows((lvl - 1) * W + g0, hin_np)
+                eng.eval_level(wires, levels[lvl - 1])
+                wires.read_rows(lvl * W + g0, hout2[s & 1])
+                return
+            wires.write_rows_async((lvl - 1) * W + g0, hin_np)   # H2D: this rank's share of the level's input wires
             exchange(lvl - 1)                                  # inputs visible on every rank
             eng.eval_level(wires, levels[lvl - 1])
             exchange(lvl)                                      # outputs visible on every rank
-            wires.read_rows(lvl * W + g0, hout_np)             # D2H: this rank's output ciphertexts (syncs)
+            wires.read_rows_async(lvl * W + g0, hout2[s & 1])  # D2H: this rank's output ciphertexts
         for s in range(args.warmup):
-            step_e2e(0)
+            step_e2e(s)
+        eng.io_sync()
         barrier()
         t0 = time.perf_counter()
         e0.record(ext)
         for s in range(args.steps):
-            step_e2e(0)
+            step_e2e(s)
+        eng.io_sync()                                          # the last download has landed in host memory
         e1.record(ext)
         barrier()
         wall = (time.perf_counter() - t0) * 1e3
         t = torch.tensor([max(e0.elapsed_time(e1), wall)], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ops1, i0, i1 = synth_level(1, W)
+        last_s = args.steps - 1
+        hout_np = hout2[last_s & 1]
+        ops1, i0, i1 = synth_level(e2e_level(last_s), W)
         ns = min(Wr, 1024)
         ok = np.array_equal(K.dec_bool_batch(hout_np[:ns]), plain_gate(ops1, bits0[i0], bits0[i1])[g0:g0 + ns])
         if not ok:
@@ -536,6 +555,9 @@ def main():
                "h2d_bytes_per_step": int(world * (hin_np.nbytes + levels[0].nbytes)), "d2h_bytes_per_step": int(world * hout_np.nbytes),
                "per_rank": "each of the %d rank(s) copies 1/%d of the level's inputs up and its own outputs down; byte counts "
                            "are the whole job's" % (world, world),
+               "pipeline": "synchronous row IO (one process, several devices)" if group else
+                           "hb_wires_write_rows_async / hb_wires_read_rows_async: the copies of neighbouring steps overlap the evaluation "
+                           "(copy stream); every step's copies are inside the timed region, which ends after hb_io_sync",
                "ms_per_step": float(t.item()) / args.steps}
 
     # ---- CPU baseline (rank 0, N = 1 only): bounded sample of level 1 on the host cores

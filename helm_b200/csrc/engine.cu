@@ -97,6 +97,10 @@ struct hb_ctx {
     hb_stats_t stats{};
     std::string err;
     int sm_count = 0;
+    // asynchronous row IO (hb_wires_*_rows_async): copy stream, its staging buffers, the two ordering events
+    cudaStream_t io_stream = nullptr;
+    cudaEvent_t io_written = nullptr, io_computed = nullptr;
+    DevBuf io_in, io_out;
     int cluster_cap = -1;                  // resident clusters of the cluster-split kernel on this device (-1: not asked yet)
     // multi-device group (hb_ctx_create_multi): the group context owns one ordinary context per device and fans every call
     // out; `level_ev` of a member = "my share of the current level is evaluated and pushed to every peer"
@@ -328,12 +332,15 @@ struct Inst16 {
     static constexpr Shape shape() { return Shape{(int)sizeof(T) * 8, 512, K, L, 16, 16, G, C::NT, &smem, &launch, &Inst<T, 512, K, L, 16, 16, 1, 32, 1>::bsk_fft, BL}; }
 };
 
+#ifndef HB_PBS3C_NT
+#define HB_PBS3C_NT 128        // threads per CTA of the cluster kernel (A/B switch)
+#endif
 const Shape g_shapes[] = {
     // tfhe boolean DEFAULT_PARAMETERS
     // pbs3 measured per shape (tests/tools/narrow_sweep.py, 100 bootstraps): boolean 2.63 vs 2.50 ms and M1C1 2.02 vs 1.97 ms (slower: on one
     // SM the N = 512 step is bound by shared-memory bandwidth and the FP64 pipe, not by the chain length), M2C2 3.34 vs 5.00 ms, multi-bit
     // 3.05 vs 4.27 ms (faster) => used for the N = 2048 shapes; -DHB_PBS3_ALL builds it for every shape (A/B)
-    with_cluster<Inst3c<uint32_t, 512, 2, 3, 4, 16, 128>>(
+    with_cluster<Inst3c<uint32_t, 512, 2, 3, 4, 16, HB_PBS3C_NT>>(
 #ifdef HB_PBS3_ALL
     with_small3<Inst3<uint32_t, 512, 2, 3, 4, 16, 384, true>>(
 #else
@@ -701,6 +708,8 @@ hb_status hb_ctx_destroy(hb_ctx* c) {
     }
     for (auto& ev : c->ev) cudaEventDestroy(ev);
     if (c->level_ev) cudaEventDestroy(c->level_ev);
+    if (c->io_stream) { cudaStreamSynchronize(c->io_stream); cudaStreamDestroy(c->io_stream); cudaEventDestroy(c->io_written); cudaEventDestroy(c->io_computed); }
+    c->io_in.release(); c->io_out.release();
     cudaStreamDestroy(c->stream);
     delete c;
     return HB_OK;
@@ -1496,4 +1505,71 @@ extern "C" hb_status hb_keyswitch_batch_noalloc(hb_ctx* c, const void* lwe_in_de
     CU(c, noalloc_scratch_ptr(c->device, &scratch));
     return c->p.torus_bits == 32 ? ks_noalloc_t<uint32_t>(c, lwe_in_dev, count, lwe_out_dev, scratch)
                                  : ks_noalloc_t<uint64_t>(c, lwe_in_dev, count, lwe_out_dev, scratch);
+}
+
+// ================================================================ asynchronous row IO
+// Pipelined serving loops: the host -> device copy of batch s+1 and the device -> host copy of batch s-1 run on the context's copy stream
+// while batch s is evaluated on its compute stream (the reference stages every level synchronously, src/circuit.rs:745-761, 877-892).
+namespace {
+hb_status io_setup(hb_ctx* c) {
+    if (c->io_stream) return HB_OK;
+    CU(c, cudaStreamCreateWithFlags(&c->io_stream, cudaStreamNonBlocking));
+    CU(c, cudaEventCreateWithFlags(&c->io_written, cudaEventDisableTiming));
+    CU(c, cudaEventCreateWithFlags(&c->io_computed, cudaEventDisableTiming));
+    return HB_OK;
+}
+template <class T> void io_repack(T* dst, uint32_t dstride, const T* src, uint32_t sstride, uint32_t cnt, uint32_t words, cudaStream_t st) {
+    const dim3 grid((words + 255) / 256, cnt < 65535 ? cnt : 65535);
+    repack_rows<T><<<grid, 256, 0, st>>>(dst, dstride, src, sstride, cnt, words);
+}
+}  // namespace
+
+extern "C" hb_status hb_wires_write_rows_async(hb_wires* w, uint32_t first, uint32_t cnt, const void* host) {
+    if (!w || (!host && cnt)) return HB_ERR_ARG;
+    hb_ctx* c = w->ctx;
+    if (c->is_group()) return fail(c, HB_ERR_UNSUPPORTED, "asynchronous row IO: single-device contexts only");
+    if (!cnt) return HB_OK;
+    if ((uint64_t)first + cnt > w->n_wires) return fail(c, HB_ERR_ARG, "wire row range out of bounds");
+    CU(c, cudaSetDevice(c->device));
+    if (hb_status s = io_setup(c)) return s;
+    const size_t ts = tsize(c), words = ct_words(c), stride = hb_wire_stride(c), bytes = (size_t)cnt * words * ts;
+    if (c->io_in.cap < bytes) { CU(c, cudaStreamSynchronize(c->io_stream)); CU(c, c->io_in.ensure(bytes)); }
+    char* drow = (char*)w->dev + (size_t)first * stride * ts;
+    CU(c, cudaMemcpyAsync(c->io_in.p, host, bytes, cudaMemcpyHostToDevice, c->io_stream));
+    if (ts == 4) io_repack<uint32_t>((uint32_t*)drow, (uint32_t)stride, (const uint32_t*)c->io_in.p, (uint32_t)words, cnt, (uint32_t)words, c->io_stream);
+    else io_repack<uint64_t>((uint64_t*)drow, (uint32_t)stride, (const uint64_t*)c->io_in.p, (uint32_t)words, cnt, (uint32_t)words, c->io_stream);
+    CU(c, cudaGetLastError());
+    c->stats.kernel_launches++;
+    CU(c, cudaEventRecord(c->io_written, c->io_stream));
+    CU(c, cudaStreamWaitEvent(c->stream, c->io_written, 0));           // everything enqueued on the compute stream from here on sees the rows
+    return HB_OK;
+}
+
+extern "C" hb_status hb_wires_read_rows_async(hb_wires* w, uint32_t first, uint32_t cnt, void* host) {
+    if (!w || (!host && cnt)) return HB_ERR_ARG;
+    hb_ctx* c = w->ctx;
+    if (c->is_group()) return fail(c, HB_ERR_UNSUPPORTED, "asynchronous row IO: single-device contexts only");
+    if (!cnt) return HB_OK;
+    if ((uint64_t)first + cnt > w->n_wires) return fail(c, HB_ERR_ARG, "wire row range out of bounds");
+    CU(c, cudaSetDevice(c->device));
+    if (hb_status s = io_setup(c)) return s;
+    const size_t ts = tsize(c), words = ct_words(c), stride = hb_wire_stride(c), bytes = (size_t)cnt * words * ts;
+    if (c->io_out.cap < bytes) { CU(c, cudaStreamSynchronize(c->io_stream)); CU(c, c->io_out.ensure(bytes)); }
+    const char* drow = (const char*)w->dev + (size_t)first * stride * ts;
+    CU(c, cudaEventRecord(c->io_computed, c->stream));                   // the rows as of the work enqueued so far
+    CU(c, cudaStreamWaitEvent(c->io_stream, c->io_computed, 0));
+    if (ts == 4) io_repack<uint32_t>((uint32_t*)c->io_out.p, (uint32_t)words, (const uint32_t*)drow, (uint32_t)stride, cnt, (uint32_t)words, c->io_stream);
+    else io_repack<uint64_t>((uint64_t*)c->io_out.p, (uint32_t)words, (const uint64_t*)drow, (uint32_t)stride, cnt, (uint32_t)words, c->io_stream);
+    CU(c, cudaGetLastError());
+    c->stats.kernel_launches++;
+    CU(c, cudaMemcpyAsync(host, c->io_out.p, bytes, cudaMemcpyDeviceToHost, c->io_stream));
+    return HB_OK;
+}
+
+extern "C" hb_status hb_io_sync(hb_ctx* c) {
+    if (!c) return HB_ERR_ARG;
+    if (c->is_group() || !c->io_stream) return HB_OK;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaStreamSynchronize(c->io_stream));
+    return HB_OK;
 }

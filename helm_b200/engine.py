@@ -46,7 +46,7 @@ assert SOP_DTYPE.itemsize == 40 and SOP_DTYPE.fields["in"][1] == 8 and SOP_DTYPE
 
 EXPORTS = ["hb_ctx_create", "hb_ctx_create_multi", "hb_ctx_destroy", "hb_last_error", "hb_set_params", "hb_load_bsk", "hb_load_ksk",
            "hb_wires_create", "hb_wires_attach", "hb_wires_destroy", "hb_ct_words", "hb_wire_stride",
-           "hb_wires_device_ptr", "hb_wires_write", "hb_wires_read", "hb_wires_write_rows", "hb_wires_read_rows", "hb_wires_set_trivial", "hb_eval_level", "hb_eval_shortint_ops",
+           "hb_wires_device_ptr", "hb_wires_write", "hb_wires_read", "hb_wires_write_rows", "hb_wires_read_rows", "hb_wires_write_rows_async", "hb_wires_read_rows_async", "hb_io_sync", "hb_wires_set_trivial", "hb_eval_level", "hb_eval_shortint_ops",
            "hb_sync", "hb_stats", "hb_stream", "hb_pbs_batch", "hb_keyswitch_batch", "hb_keyswitch_batch_noalloc",
            "hb_measure_fp64_peak"]
 
@@ -86,6 +86,9 @@ def lib():
         L.hb_wires_read.argtypes = [vp, vp, u32, vp]
         L.hb_wires_write_rows.argtypes = [vp, u32, u32, vp]
         L.hb_wires_read_rows.argtypes = [vp, u32, u32, vp]
+        L.hb_wires_write_rows_async.argtypes = [vp, u32, u32, vp]
+        L.hb_wires_read_rows_async.argtypes = [vp, u32, u32, vp]
+        L.hb_io_sync.argtypes = [vp]
         L.hb_wires_set_trivial.argtypes = [vp, vp, u32, vp]
         L.hb_eval_level.argtypes = [vp, vp, vp, u32]
         L.hb_eval_shortint_ops.argtypes = [vp, vp, vp, u32]
@@ -182,6 +185,9 @@ class Engine:
     def sync(self):
         self._ck(self.L.hb_sync(self.h), "hb_sync")
 
+    def io_sync(self):
+        self._ck(self.L.hb_io_sync(self.h), "hb_io_sync")
+
     def stats(self):
         s = HbStats()
         self._ck(self.L.hb_stats(self.h, C.byref(s)), "hb_stats")
@@ -265,6 +271,16 @@ class Wires:
         assert out.dtype == self.eng.dtype and out.flags.c_contiguous and out.shape[1] == self.eng.ct_words
         self.eng._ck(self.eng.L.hb_wires_read_rows(self.h, first, out.shape[0], _ptr(out)), "hb_wires_read_rows")
         return out
+
+    def write_rows_async(self, first, cts):
+        """as write_rows, on the context's copy stream; `cts` (pinned) must stay alive until Engine.io_sync()"""
+        assert cts.dtype == self.eng.dtype and cts.flags.c_contiguous and cts.shape[1] == self.eng.ct_words
+        self.eng._ck(self.eng.L.hb_wires_write_rows_async(self.h, first, cts.shape[0], _ptr(cts)), "hb_wires_write_rows_async")
+
+    def read_rows_async(self, first, out):
+        """as read_rows, on the context's copy stream; `out` is complete after Engine.io_sync()"""
+        assert out.dtype == self.eng.dtype and out.flags.c_contiguous and out.shape[1] == self.eng.ct_words
+        self.eng._ck(self.eng.L.hb_wires_read_rows_async(self.h, first, out.shape[0], _ptr(out)), "hb_wires_read_rows_async")
 
     def set_trivial(self, idx, plaintexts):
         idx = np.ascontiguousarray(idx, dtype=np.uint32)

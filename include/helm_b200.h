@@ -111,6 +111,14 @@ hb_status hb_wires_read(hb_wires*, const uint32_t* idx, uint32_t cnt, void* lwe_
 /* contiguous rows [first, first+cnt): one strided copy straight from/to the caller's (ideally pinned) buffer */
 hb_status hb_wires_write_rows(hb_wires*, uint32_t first, uint32_t cnt, const void* lwe_host);
 hb_status hb_wires_read_rows(hb_wires*, uint32_t first, uint32_t cnt, void* lwe_host);
+/* The same row IO, asynchronous on the context's copy stream, for pipelined serving loops (the reference stages every level synchronously
+ * through host memory, src/circuit.rs:745-761, 877-892): the upload of batch s+1 and the download of batch s-1 overlap the evaluation of batch
+ * s.  write: every hb_eval_* call issued AFTER it sees the rows; read: returns the rows as of the work enqueued BEFORE it.  Host buffers
+ * (pinned for real overlap) must stay valid, and read results are complete, after hb_io_sync.  The rows of an upload in flight must not be read or
+ * written by a batch issued earlier that is still running.  Single-device contexts only. */
+hb_status hb_wires_write_rows_async(hb_wires*, uint32_t first, uint32_t cnt, const void* lwe_host);
+hb_status hb_wires_read_rows_async(hb_wires*, uint32_t first, uint32_t cnt, void* lwe_host);
+hb_status hb_io_sync(hb_ctx*);
 hb_status hb_wires_set_trivial(hb_wires*, const uint32_t* idx, uint32_t cnt, const uint64_t* plaintext);
 
 /* evaluate every gate of one level as one batched launch sequence (asynchronous on the ctx stream).
