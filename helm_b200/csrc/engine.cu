@@ -98,7 +98,7 @@ struct hb_ctx {
     std::string err;
     int sm_count = 0;
     // asynchronous row IO (hb_wires_*_rows_async): copy stream, its staging buffers, the two ordering events
-    cudaStream_t io_stream = nullptr;
+    cudaStream_t io_stream = nullptr, io_down = nullptr;   // uploads / downloads: separate streams, so that the upload of batch s+1 does not queue behind the download of batch s
     cudaEvent_t io_written = nullptr, io_computed = nullptr;
     DevBuf io_in, io_out;
     int cluster_cap = -1;                  // resident clusters of the cluster-split kernel on this device (-1: not asked yet)
@@ -708,7 +708,10 @@ hb_status hb_ctx_destroy(hb_ctx* c) {
     }
     for (auto& ev : c->ev) cudaEventDestroy(ev);
     if (c->level_ev) cudaEventDestroy(c->level_ev);
-    if (c->io_stream) { cudaStreamSynchronize(c->io_stream); cudaStreamDestroy(c->io_stream); cudaEventDestroy(c->io_written); cudaEventDestroy(c->io_computed); }
+    if (c->io_stream) {
+        cudaStreamSynchronize(c->io_stream); cudaStreamSynchronize(c->io_down);
+        cudaStreamDestroy(c->io_stream); cudaStreamDestroy(c->io_down); cudaEventDestroy(c->io_written); cudaEventDestroy(c->io_computed);
+    }
     c->io_in.release(); c->io_out.release();
     cudaStreamDestroy(c->stream);
     delete c;
@@ -1514,6 +1517,7 @@ namespace {
 hb_status io_setup(hb_ctx* c) {
     if (c->io_stream) return HB_OK;
     CU(c, cudaStreamCreateWithFlags(&c->io_stream, cudaStreamNonBlocking));
+    CU(c, cudaStreamCreateWithFlags(&c->io_down, cudaStreamNonBlocking));
     CU(c, cudaEventCreateWithFlags(&c->io_written, cudaEventDisableTiming));
     CU(c, cudaEventCreateWithFlags(&c->io_computed, cudaEventDisableTiming));
     return HB_OK;
@@ -1554,15 +1558,15 @@ extern "C" hb_status hb_wires_read_rows_async(hb_wires* w, uint32_t first, uint3
     CU(c, cudaSetDevice(c->device));
     if (hb_status s = io_setup(c)) return s;
     const size_t ts = tsize(c), words = ct_words(c), stride = hb_wire_stride(c), bytes = (size_t)cnt * words * ts;
-    if (c->io_out.cap < bytes) { CU(c, cudaStreamSynchronize(c->io_stream)); CU(c, c->io_out.ensure(bytes)); }
+    if (c->io_out.cap < bytes) { CU(c, cudaStreamSynchronize(c->io_down)); CU(c, c->io_out.ensure(bytes)); }
     const char* drow = (const char*)w->dev + (size_t)first * stride * ts;
     CU(c, cudaEventRecord(c->io_computed, c->stream));                   // the rows as of the work enqueued so far
-    CU(c, cudaStreamWaitEvent(c->io_stream, c->io_computed, 0));
-    if (ts == 4) io_repack<uint32_t>((uint32_t*)c->io_out.p, (uint32_t)words, (const uint32_t*)drow, (uint32_t)stride, cnt, (uint32_t)words, c->io_stream);
-    else io_repack<uint64_t>((uint64_t*)c->io_out.p, (uint32_t)words, (const uint64_t*)drow, (uint32_t)stride, cnt, (uint32_t)words, c->io_stream);
+    CU(c, cudaStreamWaitEvent(c->io_down, c->io_computed, 0));
+    if (ts == 4) io_repack<uint32_t>((uint32_t*)c->io_out.p, (uint32_t)words, (const uint32_t*)drow, (uint32_t)stride, cnt, (uint32_t)words, c->io_down);
+    else io_repack<uint64_t>((uint64_t*)c->io_out.p, (uint32_t)words, (const uint64_t*)drow, (uint32_t)stride, cnt, (uint32_t)words, c->io_down);
     CU(c, cudaGetLastError());
     c->stats.kernel_launches++;
-    CU(c, cudaMemcpyAsync(host, c->io_out.p, bytes, cudaMemcpyDeviceToHost, c->io_stream));
+    CU(c, cudaMemcpyAsync(host, c->io_out.p, bytes, cudaMemcpyDeviceToHost, c->io_down));
     return HB_OK;
 }
 
@@ -1571,5 +1575,6 @@ extern "C" hb_status hb_io_sync(hb_ctx* c) {
     if (c->is_group() || !c->io_stream) return HB_OK;
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaStreamSynchronize(c->io_stream));
+    CU(c, cudaStreamSynchronize(c->io_down));
     return HB_OK;
 }
