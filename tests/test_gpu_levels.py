@@ -168,3 +168,41 @@ def test_async_row_io_pipeline_matches_synchronous(keys_factory, engine_factory)
         w.read_rows((2 * s + 1) * W, ref)
         assert np.array_equal(got, ref)
     w.close()
+
+
+@pytest.mark.parametrize("name,width", [("toy32", 48), ("boolean_default", 40)])
+def test_cluster_kernel_repeatable_and_bit_exact(name, width, keys_factory, engine_factory, oracle_mod):
+    """The narrowest levels run one bootstrap per cluster of K+1 SMs (pbs3c_kernel: partial spectra exchanged through distributed
+    shared memory with byte-counted mbarriers and double-buffered receive slots).  compute-sanitizer is not available on the pool, so
+    the exchange protocol is checked by determinism: 25 launches of the same level, including MUX gates (two bootstraps each) and a
+    ragged width, must give the same words every time, equal to the oracle's exact-integer back-end."""
+    from helm_b200 import engine as E
+    K, eng = keys_factory(name), engine_factory(name)
+    W = width
+    rng = np.random.default_rng(31)
+    bits = rng.integers(0, 2, size=(W, 3))
+    ops = rng.choice([E.AND, E.NAND, E.OR, E.NOR, E.XOR, E.XNOR, E.MUX], size=W).astype(np.uint8)
+    ops[: W // 8] = E.MUX
+    n_pbs = W + int((ops == E.MUX).sum())
+    while n_pbs > 48:                                # keep the launch inside the cluster kernel's batch limit
+        ops[np.nonzero(ops == E.MUX)[0][0]] = E.AND
+        n_pbs -= 1
+    cts = K.enc_bool_batch(bits.reshape(-1), 60600)
+    w = eng.wires(4 * W)
+    w.write_rows(0, cts)
+    ar = np.arange(W)
+    gates = E.make_gates(ops, 3 * ar, 3 * ar + 1, 3 * W + ar, in2=3 * ar + 2)
+    first = None
+    for rep in range(25):
+        eng.eval_level(w, gates)
+        eng.sync()
+        got = np.zeros((W, eng.ct_words), dtype=eng.dtype)
+        w.read_rows(3 * W, got)
+        if first is None:
+            first = got
+        assert np.array_equal(got, first), "launch %d differs from launch 0" % rep
+    ng = min(W, 12 if name == "boolean_default" else W)
+    for g in range(ng):
+        want = K.bool_gate(int(ops[g]), cts[3 * g], cts[3 * g + 1], cts[3 * g + 2], mode=oracle_mod.EXACT)
+        assert np.array_equal(first[g], want), "gate %d op %d differs from the oracle" % (g, ops[g])
+    w.close()
