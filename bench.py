@@ -241,6 +241,7 @@ def iscas_latency(name, device, params=PARAM_SET):
     sess = H.Session(params, device=device, seed=5)
     want = circ.evaluate()
     best = None
+    lv0 = sess.stats()["levels"]
     for rep in range(8):
         got, secs = sess.run(circ)
         assert all(bool(got[k]) == bool(want[k]) for k in got), "c7552: decrypted outputs differ from the plaintext netlist"
@@ -248,7 +249,8 @@ def iscas_latency(name, device, params=PARAM_SET):
     widths = circ.level_widths()
     pbs = circ.count(H.Circuit.PBS_GATES) + sum(1 for g in circ.gates() if g[1] == "mux")
     sess.close()
-    return {"netlist": name, "params": params, "levels": len(widths), "max_width": max(widths), "pbs": pbs,
+    batches = (sess.stats()["levels"] - lv0) // 8          # hb_eval_level calls per evaluation: NOT / BUF folded into their consumers
+    return {"netlist": name, "params": params, "levels": len(widths), "batches": int(batches), "max_width": max(widths), "pbs": pbs,
             "evaluate_ms": 1e3 * best[1], "encrypt_ms": 1e3 * best[0], "decrypt_ms": 1e3 * best[2],
             "pbs_per_s": pbs / best[1], "inputs": "all false", "outputs_verified": True}
 

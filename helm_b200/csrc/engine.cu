@@ -1077,7 +1077,8 @@ hb_status hb_eval_level(hb_ctx* c, hb_wires* w, const hb_gate* gates, uint32_t n
                 case HB_AND: case HB_NAND: case HB_OR: case HB_NOR: case HB_XOR: case HB_XNOR: {
                     if (!chk(G.in[0]) || !chk(G.in[1])) return fail(c, HB_ERR_ARG, "gate input wire out of range");
                     const BoolLin bl = bool_lin(G.op);
-                    PbsJob j{}; j.src0 = G.in[0]; j.src1 = G.in[1]; j.c0 = j.c1 = bl.c;
+                    PbsJob j{}; j.src0 = G.in[0]; j.src1 = G.in[1];
+                    j.c0 = (G.flags & 1) ? -bl.c : bl.c; j.c1 = (G.flags & 2) ? -bl.c : bl.c;     // flags: input taken negated (folded NOT)
                     j.cst = (uint64_t)(bl.cst_eighths * (int64_t)eighth) & tmask;
                     j.dst = (uint32_t)pj.size(); j.tv_kind = 0; j.tv_cst = eighth;
                     KsJob k{}; k.src[0] = j.dst; k.c[0] = 1; k.dst = G.out;
@@ -1086,10 +1087,11 @@ hb_status hb_eval_level(hb_ctx* c, hb_wires* w, const hb_gate* gates, uint32_t n
                 }
                 case HB_MUX: {   // then=in[0], else=in[1], select=in[2]  (reference src/gates.rs:265)
                     if (!chk(G.in[0]) || !chk(G.in[1]) || !chk(G.in[2])) return fail(c, HB_ERR_ARG, "gate input wire out of range");
-                    PbsJob a{}; a.src0 = G.in[2]; a.src1 = G.in[0]; a.c0 = 1; a.c1 = 1;
+                    const int st = (G.flags & 1) ? -1 : 1, se = (G.flags & 2) ? -1 : 1, ss = (G.flags & 4) ? -1 : 1;   // then / else / select negated
+                    PbsJob a{}; a.src0 = G.in[2]; a.src1 = G.in[0]; a.c0 = ss; a.c1 = st;
                     a.cst = (0 - eighth) & tmask; a.dst = (uint32_t)pj.size(); a.tv_kind = 0; a.tv_cst = eighth;
                     pj.push_back(a);
-                    PbsJob b{}; b.src0 = G.in[1]; b.src1 = G.in[2]; b.c0 = 1; b.c1 = -1;
+                    PbsJob b{}; b.src0 = G.in[1]; b.src1 = G.in[2]; b.c0 = se; b.c1 = -ss;
                     b.cst = (0 - eighth) & tmask; b.dst = (uint32_t)pj.size(); b.tv_kind = 0; b.tv_cst = eighth;
                     pj.push_back(b);
                     KsJob k{}; k.src[0] = a.dst; k.src[1] = b.dst; k.c[0] = 1; k.c[1] = 1; k.cst = eighth; k.dst = G.out;
@@ -1107,6 +1109,7 @@ hb_status hb_eval_level(hb_ctx* c, hb_wires* w, const hb_gate* gates, uint32_t n
         for (uint32_t g = 0; g < n_gates; ++g) {
             hb_gate G = gates[g];
             if (!chk(G.out)) return fail(c, HB_ERR_ARG, "gate output wire out of range");
+            if (G.flags) return fail(c, HB_ERR_UNSUPPORTED, "hb_gate.flags (negated inputs) need boolean (order 0) parameters");
             if (G.op == HB_COPY) {
                 if (!chk(G.in[0])) return fail(c, HB_ERR_ARG, "gate input wire out of range");
                 lj.push_back(LinJob{G.in[0], G.out, 1, 0, 0});

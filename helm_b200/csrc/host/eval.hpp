@@ -74,8 +74,15 @@ public:
     void evaluate_ready(EncWireMap& enc) override;
     WireValues decrypt_outputs(const EncWireMap& enc, bool verbose, bool latched = false) override;
     uint64_t gates_bootstrapped() const { return n_pbs_gates_; }
+    // Gates mode: NOT / BUF cost no bootstrap (ciphertext negation / copy), yet the reference's levelizer gives them a level of their own
+    // (src/circuit.rs:196-212), i.e. one more sequential batch.  With fold_linear (default; HELM_NO_FOLD=1 turns it off) a consumer
+    // reads the NOT's source wire with a negated coefficient (hb_gate.flags), so NOT / BUF add no depth; they are still evaluated (their
+    // wires are observable), as linear jobs of the batch after their source.  Results are bit-identical: -a + b is the same wrapping sum.
+    bool fold_linear = true;
+    size_t batches_per_cycle() const { return lowered_.size(); }
 protected:
     std::vector<hb_gate> lower_level(const EncWireMap& enc, const std::vector<Gate>& gates) const;
+    void lower_folded(const EncWireMap& enc);
     const ClientKey& ck_;
     const ServerKey& sk_;
     const Circuit& circuit_;

@@ -108,7 +108,7 @@ def _ptr(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
 
-def make_gates(ops, in0, in1, out, in2=None, in3=None, lut=None, arity=None):
+def make_gates(ops, in0, in1, out, in2=None, in3=None, lut=None, arity=None, flags=None):
     """Pack parallel arrays into an hb_gate[] numpy array."""
     g = np.zeros(len(ops), dtype=GATE_DTYPE)
     g["op"] = ops
@@ -123,6 +123,8 @@ def make_gates(ops, in0, in1, out, in2=None, in3=None, lut=None, arity=None):
         g["lut"] = lut
     if arity is not None:
         g["arity"] = arity
+    if flags is not None:
+        g["flags"] = flags
     return g
 
 

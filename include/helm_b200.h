@@ -57,7 +57,8 @@ enum { HB_AND = 0, HB_NAND, HB_OR, HB_NOR, HB_XOR, HB_XNOR, HB_MUX, HB_NOT, HB_C
 typedef struct {
     uint8_t op;          /* HB_* */
     uint8_t arity;       /* LUT: number of inputs (1..4) */
-    uint16_t flags;
+    uint16_t flags;      /* bit s: input s is taken NEGATED (boolean parameter sets only): a NOT gate folded into its consumer, so that NOT
+                            levels (src/circuit.rs:196-212 counts NOT as a level) cost no extra batch; 0 otherwise */
     uint32_t in[4];      /* wire indices; MUX: in[0]=then, in[1]=else, in[2]=select (src/gates.rs:265) */
     uint32_t out;        /* wire index */
     uint64_t lut;        /* LUT: truth table, bit i = output for index i; index = sum in[j] << (arity-1-j)

@@ -206,3 +206,35 @@ def test_cluster_kernel_repeatable_and_bit_exact(name, width, keys_factory, engi
         want = K.bool_gate(int(ops[g]), cts[3 * g], cts[3 * g + 1], cts[3 * g + 2], mode=oracle_mod.EXACT)
         assert np.array_equal(first[g], want), "gate %d op %d differs from the oracle" % (g, ops[g])
     w.close()
+
+
+def test_negated_input_flags_equal_explicit_not(keys_factory, engine_factory, oracle_mod):
+    """hb_gate.flags bit s = input s taken negated (a NOT folded into its consumer): the ciphertext must equal, word for word, the
+    oracle's gate on the explicitly negated input -- every gate type, every flag combination."""
+    from helm_b200 import engine as E
+    K, eng = keys_factory("toy32"), engine_factory("toy32")
+    ops, flags = [], []
+    for op in (E.AND, E.NAND, E.OR, E.NOR, E.XOR, E.XNOR):
+        for f in range(4):
+            ops.append(op); flags.append(f)
+    for f in range(8):
+        ops.append(E.MUX); flags.append(f)
+    ng = len(ops)
+    rng = np.random.default_rng(41)
+    bits = rng.integers(0, 2, size=(ng, 3))
+    cts = K.enc_bool_batch(bits.reshape(-1), 31300)
+    w = eng.wires(4 * ng)
+    w.write_rows(0, cts)
+    ar = np.arange(ng)
+    eng.eval_level(w, E.make_gates(ops, 3 * ar, 3 * ar + 1, 3 * ng + ar, in2=3 * ar + 2, flags=flags))
+    eng.sync()
+    got = np.zeros((ng, eng.ct_words), dtype=eng.dtype)
+    w.read_rows(3 * ng, got)
+    neg = lambda c: (np.zeros_like(c) - c).astype(K.dtype)
+    for g in range(ng):
+        a, b, c = (neg(cts[3 * g + s]) if (flags[g] >> s) & 1 else cts[3 * g + s] for s in range(3))
+        want = K.bool_gate(int(ops[g]), a, b, c, mode=oracle_mod.EXACT)
+        assert np.array_equal(got[g], want), "op %d flags %d" % (ops[g], flags[g])
+        x, y, s = (int(bits[g, q]) ^ ((flags[g] >> q) & 1) for q in range(3))
+        assert K.dec_bool(got[g]) == bool(_plain(E, int(ops[g]), x, y, s))
+    w.close()
