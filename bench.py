@@ -514,6 +514,11 @@ def main():
             hb2 = torch.empty((Wr, words), dtype=torch.int32).pin_memory()
             hout2 = [hout_np, hb2.numpy().view(eng.dtype)]
 
+        io_ext = torch.cuda.ExternalStream(eng.io_stream(), device=torch.device("cuda", local)) if (world > 1 and not group) else None
+        # its own communicator: NCCL serialises the collectives of one communicator, and the all-gather of step s+1's inputs must not
+        # queue behind the all-gather of step s's outputs (which waits for the evaluation of step s)
+        in_group = dist.new_group() if io_ext is not None else None
+
         def e2e_level(s):
             # inputs in an even block, outputs in the odd block after it: consecutive steps touch disjoint rows, so the upload of step
             # s+1 and the download of step s-1 (copy stream) may overlap the evaluation of step s (compute stream)
@@ -527,7 +532,10 @@ def main():
                 wires.read_rows(lvl * W + g0, hout2[s & 1])
                 return
             wires.write_rows_async((lvl - 1) * W + g0, hin_np)   # H2D: this rank's share of the level's input wires
-            exchange(lvl - 1)                                  # inputs visible on every rank
+            if world > 1:                                      # inputs visible on every rank: all-gather on the UPLOAD stream, so that
+                with torch.cuda.stream(io_ext):                # it overlaps the previous step's evaluation, then a fence for the compute stream
+                    shard.exchange_level(dist, wt[(lvl - 1) * W:lvl * W], world, rank, group=in_group)
+                eng.io_fence()
             eng.eval_level(wires, levels[lvl - 1])
             exchange(lvl)                                      # outputs visible on every rank
             wires.read_rows_async(lvl * W + g0, hout2[s & 1])  # D2H: this rank's output ciphertexts

@@ -1573,6 +1573,24 @@ extern "C" hb_status hb_wires_read_rows_async(hb_wires* w, uint32_t first, uint3
     return HB_OK;
 }
 
+// the upload stream (cudaStream_t as void*): a caller that has to post-process uploaded rows before they are evaluated (the all-gather of
+// the ranks' input shares in a one-process-per-GPU deployment) enqueues that work here, then calls hb_io_fence
+extern "C" void* hb_io_stream(hb_ctx* c) {
+    if (!c || c->is_group()) return nullptr;
+    if (cudaSetDevice(c->device) != cudaSuccess || io_setup(c) != HB_OK) return nullptr;
+    return (void*)c->io_stream;
+}
+// everything enqueued on the upload stream so far happens before every hb_eval_* call issued after this
+extern "C" hb_status hb_io_fence(hb_ctx* c) {
+    if (!c) return HB_ERR_ARG;
+    if (c->is_group()) return fail(c, HB_ERR_UNSUPPORTED, "asynchronous row IO: single-device contexts only");
+    CU(c, cudaSetDevice(c->device));
+    if (hb_status s = io_setup(c)) return s;
+    CU(c, cudaEventRecord(c->io_written, c->io_stream));
+    CU(c, cudaStreamWaitEvent(c->stream, c->io_written, 0));
+    return HB_OK;
+}
+
 extern "C" hb_status hb_io_sync(hb_ctx* c) {
     if (!c) return HB_ERR_ARG;
     if (c->is_group() || !c->io_stream) return HB_OK;

@@ -46,7 +46,7 @@ assert SOP_DTYPE.itemsize == 40 and SOP_DTYPE.fields["in"][1] == 8 and SOP_DTYPE
 
 EXPORTS = ["hb_ctx_create", "hb_ctx_create_multi", "hb_ctx_destroy", "hb_last_error", "hb_set_params", "hb_load_bsk", "hb_load_ksk",
            "hb_wires_create", "hb_wires_attach", "hb_wires_destroy", "hb_ct_words", "hb_wire_stride",
-           "hb_wires_device_ptr", "hb_wires_write", "hb_wires_read", "hb_wires_write_rows", "hb_wires_read_rows", "hb_wires_write_rows_async", "hb_wires_read_rows_async", "hb_io_sync", "hb_wires_set_trivial", "hb_eval_level", "hb_eval_shortint_ops",
+           "hb_wires_device_ptr", "hb_wires_write", "hb_wires_read", "hb_wires_write_rows", "hb_wires_read_rows", "hb_wires_write_rows_async", "hb_wires_read_rows_async", "hb_io_sync", "hb_io_stream", "hb_io_fence", "hb_wires_set_trivial", "hb_eval_level", "hb_eval_shortint_ops",
            "hb_sync", "hb_stats", "hb_stream", "hb_pbs_batch", "hb_keyswitch_batch", "hb_keyswitch_batch_noalloc",
            "hb_measure_fp64_peak"]
 
@@ -89,6 +89,9 @@ def lib():
         L.hb_wires_write_rows_async.argtypes = [vp, u32, u32, vp]
         L.hb_wires_read_rows_async.argtypes = [vp, u32, u32, vp]
         L.hb_io_sync.argtypes = [vp]
+        L.hb_io_stream.restype = vp
+        L.hb_io_stream.argtypes = [vp]
+        L.hb_io_fence.argtypes = [vp]
         L.hb_wires_set_trivial.argtypes = [vp, vp, u32, vp]
         L.hb_eval_level.argtypes = [vp, vp, vp, u32]
         L.hb_eval_shortint_ops.argtypes = [vp, vp, vp, u32]
@@ -186,6 +189,12 @@ class Engine:
 
     def sync(self):
         self._ck(self.L.hb_sync(self.h), "hb_sync")
+
+    def io_stream(self):
+        return self.L.hb_io_stream(self.h)
+
+    def io_fence(self):
+        self._ck(self.L.hb_io_fence(self.h), "hb_io_fence")
 
     def io_sync(self):
         self._ck(self.L.hb_io_sync(self.h), "hb_io_sync")

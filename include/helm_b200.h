@@ -120,6 +120,10 @@ hb_status hb_wires_read_rows(hb_wires*, uint32_t first, uint32_t cnt, void* lwe_
 hb_status hb_wires_write_rows_async(hb_wires*, uint32_t first, uint32_t cnt, const void* lwe_host);
 hb_status hb_wires_read_rows_async(hb_wires*, uint32_t first, uint32_t cnt, void* lwe_host);
 hb_status hb_io_sync(hb_ctx*);
+/* the upload stream of the context (cudaStream_t as void*) and a fence: work a caller enqueues on that stream after an asynchronous upload
+ * (one process per GPU: the all-gather of the ranks' input shares) is ordered before every hb_eval_* call issued after hb_io_fence */
+void* hb_io_stream(hb_ctx*);
+hb_status hb_io_fence(hb_ctx*);
 hb_status hb_wires_set_trivial(hb_wires*, const uint32_t* idx, uint32_t cnt, const uint64_t* plaintext);
 
 /* evaluate every gate of one level as one batched launch sequence (asynchronous on the ctx stream).
