@@ -84,6 +84,7 @@ int64_t hh_circuit_count(const hh_circuit* c, int what) {
                   for (const auto& lv : c->c->levels()) for (const auto& g : lv)
                       n += !(g.type == GateType::Not || g.type == GateType::Buf || g.type == GateType::Dff || g.type == GateType::Copy);
                   return n; }
+        case 9: return c->c->netlist().has_luts || c->c->netlist().has_arith ? (int64_t)c->c->levels().size() : (int64_t)c->c->folded_batches().size();
     }
     return -1;
 }

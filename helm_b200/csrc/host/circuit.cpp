@@ -167,3 +167,58 @@ WireValues Circuit::evaluate(const WireValues& wire_map, unsigned int_bits) cons
 }
 
 }  // namespace helm
+
+namespace helm {
+
+std::vector<std::vector<Circuit::FoldedGate>> Circuit::folded_batches() const {
+    if (!levelled_) throw Error("folded_batches: compute_levels has not run");
+    std::unordered_map<std::string, const Gate*> producer;
+    for (size_t li = 0; li < levels_.size(); ++li)
+        if (li != dff_level_) for (const Gate& g : levels_[li]) producer[g.output] = &g;
+    auto resolve = [&](const std::string& w0, bool* neg_out) {
+        std::string w = w0; bool neg = false;
+        for (;;) {
+            auto p = producer.find(w);
+            if (p == producer.end() || (p->second->type != GateType::Not && p->second->type != GateType::Buf)) break;
+            if (p->second->type == GateType::Not) neg = !neg;
+            w = p->second->inputs.at(0);
+        }
+        *neg_out = neg;
+        return w;
+    };
+    std::unordered_map<std::string, size_t> depth;             // of wires driven by bootstrapped gates; anything else is 0
+    auto wire_depth = [&](const std::string& w) { auto it = depth.find(w); return it == depth.end() ? (size_t)0 : it->second; };
+    std::vector<std::vector<FoldedGate>> out;
+    auto at_batch = [&](size_t d) -> std::vector<FoldedGate>& { if (out.size() < d) out.resize(d); return out[d - 1]; };
+    for (size_t li = 0; li < levels_.size(); ++li) {           // the level order is a topological order
+        if (li == dff_level_) continue;
+        for (const Gate& g : levels_[li]) {
+            FoldedGate f; f.gate = &g;
+            const bool linear = g.type == GateType::Not || g.type == GateType::Buf;
+            size_t d = 0;
+            if (linear) {
+                bool neg; const std::string src = resolve(g.output, &neg);
+                f.src.push_back(src); f.neg.push_back(neg);
+                d = wire_depth(src);
+            } else {
+                for (const auto& w : g.inputs) {
+                    bool neg; const std::string src = resolve(w, &neg);
+                    f.src.push_back(src); f.neg.push_back(neg);
+                    d = std::max(d, wire_depth(src));
+                }
+                depth[g.output] = d + 1;
+            }
+            at_batch(d + 1).push_back(std::move(f));
+        }
+    }
+    if (dff_level_ != npos) {
+        out.emplace_back();
+        for (const Gate& g : levels_[dff_level_]) {
+            FoldedGate f; f.gate = &g; f.src = g.inputs; f.neg.assign(g.inputs.size(), false);
+            out.back().push_back(std::move(f));
+        }
+    }
+    return out;
+}
+
+}  // namespace helm

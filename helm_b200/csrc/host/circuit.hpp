@@ -27,6 +27,13 @@ public:
     // plaintext reference semantics (src/gates.rs:151-239); int_bits = width of arithmetic wires (u8..u128)
     WireValues evaluate(const WireValues& wire_map, unsigned int_bits = 0) const;
 
+    // Gates-mode schedule with NOT / BUF contracted (they cost no bootstrap, yet the reference's levels count them, src/circuit.rs:196-212):
+    // every input of a gate is resolved through chains of NOT / BUF to (source wire, negated?); a bootstrapped gate sits in batch
+    // 1 + the deepest batch of its sources; a NOT / BUF is evaluated from its resolved source in the batch after that source's.  The
+    // DFF level stays last (sources as written).  gate points into levels().
+    struct FoldedGate { const Gate* gate; std::vector<std::string> src; std::vector<bool> neg; };
+    std::vector<std::vector<FoldedGate>> folded_batches() const;
+
     const Netlist& netlist() const { return nl_; }
     bool is_constant_operand(const std::string& wire) const;
 

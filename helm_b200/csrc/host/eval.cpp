@@ -150,54 +150,29 @@ std::vector<hb_gate> BatchedCircuit::lower_level(const EncWireMap& enc, const st
 // through chains of NOT / BUF; a bootstrapped gate's depth is 1 + the largest depth of its resolved sources; a NOT / BUF is evaluated
 // from its resolved source in the batch after that source's.  The DFF level stays last.
 void BatchedCircuit::lower_folded(const EncWireMap& enc) {
-    const auto& levels = circuit_.levels();
+    const auto batches = circuit_.folded_batches();
     const size_t dffl = circuit_.dff_level();
-    std::unordered_map<std::string, const Gate*> producer;
-    for (size_t li = 0; li < levels.size(); ++li)
-        if (li != dffl) for (const Gate& g : levels[li]) producer[g.output] = &g;
-    struct Res { std::string src; bool neg; };
-    std::unordered_map<std::string, Res> memo;
-    auto resolve = [&](const std::string& w0) -> Res {
-        auto it = memo.find(w0);
-        if (it != memo.end()) return it->second;
-        std::string w = w0; bool neg = false;
-        for (;;) {
-            auto p = producer.find(w);
-            if (p == producer.end() || (p->second->type != GateType::Not && p->second->type != GateType::Buf)) break;
-            if (p->second->type == GateType::Not) neg = !neg;
-            w = p->second->inputs.at(0);
-        }
-        return memo[w0] = Res{w, neg};
-    };
-    std::unordered_map<std::string, size_t> depth;             // of wires driven by bootstrapped gates; anything else is 0
-    auto wire_depth = [&](const std::string& w) { auto it = depth.find(w); return it == depth.end() ? (size_t)0 : it->second; };
     std::vector<std::vector<hb_gate>> out;
-    auto at_level = [&](size_t d) -> std::vector<hb_gate>& { if (out.size() < d) out.resize(d); return out[d - 1]; };
-    for (size_t li = 0; li < levels.size(); ++li) {            // the level order is a topological order
-        if (li == dffl) continue;
-        for (const Gate& g : levels[li]) {
+    for (size_t bi = 0; bi < batches.size(); ++bi) {
+        if (dffl != Circuit::npos && bi + 1 == batches.size()) { out.push_back(lower_level(enc, circuit_.levels()[dffl])); break; }
+        std::vector<hb_gate> hg;
+        for (const auto& f : batches[bi]) {
+            const Gate& g = *f.gate;
+            hb_gate h{};
             if (g.type == GateType::Not || g.type == GateType::Buf) {
-                const Res r = resolve(g.output);
-                hb_gate h{};
-                h.op = r.neg ? HB_NOT : HB_COPY; h.in[0] = enc.at(r.src); h.out = enc.at(g.output);
-                at_level(wire_depth(r.src) + 1).push_back(h);
-                continue;
+                h.op = f.neg.at(0) ? HB_NOT : HB_COPY; h.in[0] = enc.at(f.src.at(0)); h.out = enc.at(g.output);
+            } else {
+                h = lower_level(enc, std::vector<Gate>{g}).at(0);
+                const size_t nin = h.op == HB_MUX ? 3 : 2;        // the encrypted path uses exactly these inputs (src/gates.rs:255-271)
+                for (size_t s = 0; s < nin; ++s) {
+                    h.in[s] = enc.at(f.src.at(s));
+                    if (f.neg.at(s)) h.flags |= (uint16_t)(1u << s);
+                }
             }
-            std::vector<hb_gate> one = lower_level(enc, std::vector<Gate>{g});
-            hb_gate h = one.at(0);
-            const size_t nin = h.op == HB_MUX ? 3 : 2;
-            size_t d = 0;
-            for (size_t s = 0; s < nin; ++s) {
-                const Res r = resolve(g.inputs.at(s));
-                h.in[s] = enc.at(r.src);
-                if (r.neg) h.flags |= (uint16_t)(1u << s);
-                d = std::max(d, wire_depth(r.src));
-            }
-            depth[g.output] = d + 1;
-            at_level(d + 1).push_back(h);
+            hg.push_back(h);
         }
+        out.push_back(std::move(hg));
     }
-    if (dffl != Circuit::npos) out.push_back(lower_level(enc, levels[dffl]));
     lowered_ = std::move(out);
 }
 

@@ -111,7 +111,7 @@ def read_input_wires(path, ptxt_type="bool"):
 
 class Circuit:
     """read_verilog_file + Circuit::new + sort_circuit + compute_levels (reference src/bin/helm.rs:38-62)."""
-    GATES, WIRES, INPUTS, OUTPUTS, DFFS, LEVELS, HAS_LUTS, HAS_ARITH, PBS_GATES = range(9)
+    GATES, WIRES, INPUTS, OUTPUTS, DFFS, LEVELS, HAS_LUTS, HAS_ARITH, PBS_GATES, BATCHES = range(10)
 
     def __init__(self, path=None, text=None, is_arith=False, strict_reference_levels=False):
         self.L = lib()

@@ -24,7 +24,8 @@ int hh_circuit_load(const char* verilog_path, int is_arith, int strict_reference
 int hh_circuit_load_text(const char* verilog_text, int is_arith, int strict_reference_levels, hh_circuit** out);
 void hh_circuit_free(hh_circuit*);
 /* what: 0 gates, 1 wire_set, 2 inputs (with duplicates, DFF outputs appended), 3 outputs, 4 dff_outputs, 5 levels
- * (DFF level included), 6 has_luts, 7 has_arith, 8 bootstrapped gates (PBS gates; MUX counts once) */
+ * (DFF level included), 6 has_luts, 7 has_arith, 8 bootstrapped gates (PBS gates; MUX counts once), 9 batches of the encrypted gates-mode
+ * evaluation: levels with NOT / BUF folded into their consumers (a NOT is a level in the reference, src/circuit.rs:196-212, but no bootstrap) */
 int64_t hh_circuit_count(const hh_circuit*, int what);
 int64_t hh_circuit_level_width(const hh_circuit*, int level_index);
 /* one name per line: what = 2 declared inputs (duplicates kept, DFF outputs appended), 3 outputs, 4 dff_outputs */

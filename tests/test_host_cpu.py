@@ -181,3 +181,15 @@ def test_corpus_preprocesses_and_levelizes():
         assert c.count(C.LEVELS) >= 1 and c.evaluate()
         if name in shapes:
             assert (c.count(C.LEVELS), c.count(C.PBS_GATES)) == shapes[name], name
+
+
+def test_not_folding_batch_counts():
+    """NOT / BUF contracted out of the encrypted schedule (Circuit::folded_batches): fewer sequential batches than reference levels
+    where a NOT sits on the critical path; never more."""
+    import corpus
+    want = {"c432.v": (30, 26), "c7552.v": (31, 30), "c2670.v": (19, 18), "c880.v": (26, 26), "16-bit-mult-gates.v": (31, 31)}
+    for name, (levels, batches) in want.items():
+        c = C(text=H.preprocess_yosys(corpus.text(name), exact_consts=True))
+        assert (c.count(C.LEVELS), c.count(C.BATCHES)) == (levels, batches), name
+    s27 = C(os.path.join(NET, "s27.v"))
+    assert s27.count(C.BATCHES) <= s27.count(C.LEVELS)
