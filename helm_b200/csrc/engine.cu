@@ -101,6 +101,12 @@ struct hb_ctx {
     cudaStream_t io_stream = nullptr, io_down = nullptr;   // uploads / downloads: separate streams, so that the upload of batch s+1 does not queue behind the download of batch s
     cudaEvent_t io_written = nullptr, io_computed = nullptr;
     DevBuf io_in, io_out;
+    // CUDA-graph capture of a sequence of batches (hb_graph_begin / hb_graph_end): job descriptors go to an arena owned by the graph
+    bool capturing = false;
+    PinBuf cap_pin; DevBuf cap_dev; size_t cap_used = 0;
+    JobSlot cap_slot;                      // stand-in for the ring slot while capturing (its timing events are recorded but never read)
+    uint64_t scratch_gen = 0;              // bumped whenever a scratch buffer is reallocated: a graph captured before that is stale
+    hb_stats_t cap_stats0{};
     int cluster_cap = -1;                  // resident clusters of the cluster-split kernel on this device (-1: not asked yet)
     // multi-device group (hb_ctx_create_multi): the group context owns one ordinary context per device and fans every call
     // out; `level_ev` of a member = "my share of the current level is evaluated and pushed to every peer"
@@ -409,15 +415,38 @@ hb_status check_ready(hb_ctx* c) {
     return HB_OK;
 }
 
+hb_status ensure_scratch(hb_ctx* c, DevBuf& b, size_t bytes) {
+    if (bytes <= b.cap) return HB_OK;
+    if (c->capturing) return fail(c, HB_ERR_STATE, "graph capture: scratch buffers must be sized by an eager evaluation of the same batches first");
+    CU(c, b.ensure(bytes));
+    c->scratch_gen++;
+    return HB_OK;
+}
+
 // uploads the three job arrays of one level through a pinned ring slot; returns device pointers
 hb_status upload_jobs(hb_ctx* c, const std::vector<PbsJob>& pj, const std::vector<KsJob>& kj, const std::vector<LinJob>& lj,
                       const PbsJob** dp, const KsJob** dk, const LinJob** dl, JobSlot** slot_out) {
+    const size_t a = pj.size() * sizeof(PbsJob), b = kj.size() * sizeof(KsJob), d = lj.size() * sizeof(LinJob);
+    const size_t oa = 0, ob = (a + 15) & ~(size_t)15, od = ob + ((b + 15) & ~(size_t)15), tot = od + d + 16;
+    if (c->capturing) {
+        // recorded, not executed: the descriptors live in the graph's arena (the copy node re-reads the pinned half on every replay)
+        const size_t off = (c->cap_used + 255) & ~(size_t)255;
+        if (off + tot > c->cap_pin.cap || off + tot > c->cap_dev.cap)
+            return fail(c, HB_ERR_ARG, "graph capture: job arena too small (hb_graph_begin job_bytes)");
+        char* h = (char*)c->cap_pin.p + off; char* dv = (char*)c->cap_dev.p + off;
+        if (a) memcpy(h + oa, pj.data(), a);
+        if (b) memcpy(h + ob, kj.data(), b);
+        if (d) memcpy(h + od, lj.data(), d);
+        CU(c, cudaMemcpyAsync(dv, h, tot, cudaMemcpyHostToDevice, c->stream));
+        c->cap_used = off + tot;
+        *dp = (const PbsJob*)(dv + oa); *dk = (const KsJob*)(dv + ob); *dl = (const LinJob*)(dv + od);
+        *slot_out = &c->cap_slot;
+        return HB_OK;
+    }
     CtxExtra* ex = extra_of(c);
     JobSlot& s = ex->slots[ex->next++ % NSLOT];
     CU(c, cudaEventSynchronize(s.done));
     fold_timing(c, s, &ex->slots[ex->next % NSLOT]);
-    const size_t a = pj.size() * sizeof(PbsJob), b = kj.size() * sizeof(KsJob), d = lj.size() * sizeof(LinJob);
-    const size_t oa = 0, ob = (a + 15) & ~(size_t)15, od = ob + ((b + 15) & ~(size_t)15), tot = od + d + 16;
     if (s.pin.cap < tot || s.dev.cap < tot) {
         // grow every slot of the ring at once: otherwise the pinned / device allocations of slots 1 .. NSLOT-1 (tens of ms
         // each on a busy host) land in the second .. fourth batch, i.e. inside a caller's timed region after a short warm-up
@@ -511,7 +540,7 @@ hb_status launch_pbs(hb_ctx* c, const void* in, uint32_t in_stride, void* out, u
     const size_t smem = sh.smem(c->p.n);
     if (smem > 227 * 1024) return fail(c, HB_ERR_UNSUPPORTED, "PBS shared memory footprint exceeds 227 KB");
     a.atil_stride = (uint32_t)((c->p.n + 2 + 7) & ~7);
-    CU(c, c->atil.ensure(((size_t)n_jobs + 16) * a.atil_stride * sizeof(uint16_t)));
+    if (hb_status s = ensure_scratch(c, c->atil, ((size_t)n_jobs + 16) * a.atil_stride * sizeof(uint16_t))) return s;
     a.atil = (uint16_t*)c->atil.p;
     CU(c, sh.launch(a, c->stream, smem));
     c->stats.kernel_launches++; c->stats.pbs_count += n_jobs;
@@ -534,7 +563,7 @@ hb_status launch_ks(hb_ctx* c, const void* in, uint32_t in_stride, void* out, ui
         const int tn = c->p.torus_bits == 32 ? KmCfg<uint32_t>::TN : KmCfg<uint64_t>::TN;
         const dim3 grid((n_jobs + KM_TM - 1) / KM_TM, c->ksk_npad / tn);
         const uint32_t rows_pad = grid.x * KM_TM;
-        CU(c, c->ks_dig.ensure((size_t)rows_pad * a.kN * a.level));
+        if (hb_status s = ensure_scratch(c, c->ks_dig, (size_t)rows_pad * a.kN * a.level)) return s;
         const unsigned dg = rows_pad < 65535u ? rows_pad : 65535u;
         if (c->p.torus_bits == 32) {
             static SmemOptIn opt2;
@@ -598,7 +627,7 @@ template <class T> hb_status launch_lin_t(hb_ctx* c, void* w, uint32_t stride, c
         linear_rows<T, 0><<<grid, 256, 0, c->stream>>>((T*)w, stride, nullptr, jobs, cnt, words);
         c->stats.kernel_launches++;
     } else {
-        CU(c, c->lin_stage.ensure((size_t)cnt * stride * sizeof(T)));
+        if (hb_status s = ensure_scratch(c, c->lin_stage, (size_t)cnt * stride * sizeof(T))) return s;
         linear_rows<T, 1><<<grid, 256, 0, c->stream>>>((T*)w, stride, (T*)c->lin_stage.p, jobs, cnt, words);
         linear_rows<T, 2><<<grid, 256, 0, c->stream>>>((T*)w, stride, (T*)c->lin_stage.p, jobs, cnt, words);
         c->stats.kernel_launches += 2;
@@ -628,7 +657,7 @@ template <class T> hb_status launch_lincomb_t(hb_ctx* c, void* w, uint32_t strid
         lincomb_rows<T, 0><<<grid, 256, 0, c->stream>>>((T*)w, stride, nullptr, jobs, cnt, words);
         c->stats.kernel_launches++;
     } else {
-        CU(c, c->lin_stage.ensure((size_t)cnt * stride * sizeof(T)));
+        if (hb_status s = ensure_scratch(c, c->lin_stage, (size_t)cnt * stride * sizeof(T))) return s;
         lincomb_rows<T, 1><<<grid, 256, 0, c->stream>>>((T*)w, stride, (T*)c->lin_stage.p, jobs, cnt, words);
         lincomb_rows<T, 2><<<grid, 256, 0, c->stream>>>((T*)w, stride, (T*)c->lin_stage.p, jobs, cnt, words);
         c->stats.kernel_launches += 2;
@@ -691,6 +720,8 @@ hb_status hb_ctx_create(int32_t device, hb_ctx** out) {
         CU(nullptr, cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
         for (auto& t : s.t) CU(nullptr, cudaEventCreate(&t));
     }
+    CU(nullptr, cudaEventCreateWithFlags(&c->cap_slot.done, cudaEventDisableTiming));
+    for (auto& t : c->cap_slot.t) CU(nullptr, cudaEventCreateWithFlags(&t, cudaEventDisableTiming));
     *out = c;
     return HB_OK;
 }
@@ -707,6 +738,9 @@ hb_status hb_ctx_destroy(hb_ctx* c) {
         for (auto& t : s.t) cudaEventDestroy(t);
     }
     for (auto& ev : c->ev) cudaEventDestroy(ev);
+    cudaEventDestroy(c->cap_slot.done);
+    for (auto& t : c->cap_slot.t) cudaEventDestroy(t);
+    c->cap_pin.release(); c->cap_dev.release();
     if (c->level_ev) cudaEventDestroy(c->level_ev);
     if (c->io_stream) {
         cudaStreamSynchronize(c->io_stream); cudaStreamSynchronize(c->io_down);
@@ -987,6 +1021,7 @@ hb_status hb_sync(hb_ctx* c) {
         for (hb_ctx* m : c->subs) if (hb_status s = lift(c, m, hb_sync(m))) return s;
         return HB_OK;
     }
+    if (c->capturing) return HB_OK;                           // between hb_graph_begin and hb_graph_end nothing runs: nothing to wait for
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaStreamSynchronize(c->stream));
     return HB_OK;
@@ -1145,13 +1180,13 @@ hb_status hb_eval_level(hb_ctx* c, hb_wires* w, const hb_gate* gates, uint32_t n
     CU(c, cudaEventRecord(slot->t[0], c->stream));
     if (p.order == 0) {
         const uint32_t bstride = pad4(big_words(c));
-        CU(c, c->scratch_a.ensure((size_t)pj.size() * bstride * ts));
+        if (hb_status s = ensure_scratch(c, c->scratch_a, (size_t)pj.size() * bstride * ts)) return s;
         if (hb_status s = launch_pbs(c, w->dev, wstride, c->scratch_a.p, bstride, dp, (uint32_t)pj.size())) return s;
         CU(c, cudaEventRecord(slot->t[1], c->stream));
         if (hb_status s = launch_ks(c, c->scratch_a.p, bstride, w->dev, wstride, dk, (uint32_t)kj.size())) return s;
     } else {
         const uint32_t sstride = pad4(small_words(c));
-        CU(c, c->scratch_b.ensure((size_t)kj.size() * sstride * ts));
+        if (hb_status s = ensure_scratch(c, c->scratch_b, (size_t)kj.size() * sstride * ts)) return s;
         if (hb_status s = launch_ks(c, w->dev, wstride, c->scratch_b.p, sstride, dk, (uint32_t)kj.size())) return s;
         CU(c, cudaEventRecord(slot->t[1], c->stream));
         if (hb_status s = launch_pbs(c, c->scratch_b.p, sstride, w->dev, wstride, dp, (uint32_t)pj.size())) return s;
@@ -1203,7 +1238,7 @@ hb_status hb_eval_shortint_ops(hb_ctx* c, hb_wires* w, const hb_sop* ops, uint32
     if (!pj.empty()) {
         if (hb_status s = upload_jobs(c, pj, kj, {}, &dp, &dk, &dl, &slot)) return s;
         const uint32_t sstride = pad4(small_words(c));
-        CU(c, c->scratch_b.ensure((size_t)kj.size() * sstride * ts));
+        if (hb_status s = ensure_scratch(c, c->scratch_b, (size_t)kj.size() * sstride * ts)) return s;
         CU(c, cudaEventRecord(slot->t[0], c->stream));
         if (hb_status s = launch_ks(c, w->dev, wstride, c->scratch_b.p, sstride, dk, (uint32_t)kj.size())) return s;
         CU(c, cudaEventRecord(slot->t[1], c->stream));
@@ -1597,5 +1632,83 @@ extern "C" hb_status hb_io_sync(hb_ctx* c) {
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaStreamSynchronize(c->io_stream));
     CU(c, cudaStreamSynchronize(c->io_down));
+    return HB_OK;
+}
+
+// ================================================================ CUDA-graph capture of a batch sequence
+// A cycle of a sequential circuit issues the same batches every time: hb_graph_begin .. hb_graph_end records the hb_eval_level /
+// hb_eval_shortint_ops calls made in between (nothing runs) into one CUDA graph -- job-descriptor uploads included -- and
+// hb_graph_launch replays it with one launch.  The reference has no counterpart (its cycle loop re-issues every gate,
+// src/bin/helm.rs:256-270).
+struct hb_graph {
+    hb_ctx* ctx = nullptr;
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    PinBuf pin; DevBuf dev;                // the job arena the graph's copy nodes read / write
+    uint64_t scratch_gen = 0;
+    hb_stats_t delta{};                    // what one replay adds to the context's counters
+};
+
+extern "C" hb_status hb_graph_begin(hb_ctx* c, size_t job_bytes) {
+    if (hb_status s = check_ready(c)) return s;
+    if (c->is_group()) return fail(c, HB_ERR_UNSUPPORTED, "graph capture: single-device contexts only");
+    if (c->capturing) return fail(c, HB_ERR_STATE, "graph capture already in progress");
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaStreamSynchronize(c->stream));
+    const size_t want = job_bytes + 4096;
+    CU(c, c->cap_pin.ensure(want));
+    CU(c, c->cap_dev.ensure(want));
+    c->cap_used = 0;
+    c->cap_stats0 = c->stats;
+    CU(c, cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeRelaxed));
+    c->capturing = true;
+    return HB_OK;
+}
+
+extern "C" hb_status hb_graph_end(hb_ctx* c, hb_graph** out) {
+    if (!c || !out) return HB_ERR_ARG;
+    if (!c->capturing) return fail(c, HB_ERR_STATE, "hb_graph_end without hb_graph_begin");
+    *out = nullptr;
+    c->capturing = false;
+    cudaGraph_t g = nullptr;
+    CU(c, cudaStreamEndCapture(c->stream, &g));
+    hb_graph* hg = new hb_graph();
+    hg->ctx = c; hg->graph = g;
+    cudaError_t e = cudaGraphInstantiate(&hg->exec, g, 0);
+    if (e != cudaSuccess) { cudaGraphDestroy(g); delete hg; return fail(c, HB_ERR_CUDA, std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e)); }
+    hg->pin = c->cap_pin; hg->dev = c->cap_dev;                        // the arena now belongs to the graph
+    c->cap_pin = PinBuf(); c->cap_dev = DevBuf();
+    hg->scratch_gen = c->scratch_gen;
+    hg->delta.pbs_count = c->stats.pbs_count - c->cap_stats0.pbs_count;
+    hg->delta.ks_count = c->stats.ks_count - c->cap_stats0.ks_count;
+    hg->delta.levels = c->stats.levels - c->cap_stats0.levels;
+    hg->delta.kernel_launches = c->stats.kernel_launches - c->cap_stats0.kernel_launches;
+    c->stats.pbs_count = c->cap_stats0.pbs_count; c->stats.ks_count = c->cap_stats0.ks_count;      // nothing ran yet
+    c->stats.levels = c->cap_stats0.levels; c->stats.kernel_launches = c->cap_stats0.kernel_launches;
+    *out = hg;
+    return HB_OK;
+}
+
+extern "C" hb_status hb_graph_launch(hb_graph* g) {
+    if (!g) return HB_ERR_ARG;
+    hb_ctx* c = g->ctx;
+    if (c->capturing) return fail(c, HB_ERR_STATE, "hb_graph_launch during a capture");
+    if (g->scratch_gen != c->scratch_gen)
+        return fail(c, HB_ERR_STATE, "graph is stale: a larger batch reallocated the scratch buffers it points into; capture it again");
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaGraphLaunch(g->exec, c->stream));
+    c->stats.pbs_count += g->delta.pbs_count; c->stats.ks_count += g->delta.ks_count;
+    c->stats.levels += g->delta.levels; c->stats.kernel_launches += g->delta.kernel_launches;
+    return HB_OK;
+}
+
+extern "C" hb_status hb_graph_destroy(hb_graph* g) {
+    if (!g) return HB_ERR_ARG;
+    cudaSetDevice(g->ctx->device);
+    cudaStreamSynchronize(g->ctx->stream);
+    if (g->exec) cudaGraphExecDestroy(g->exec);
+    if (g->graph) cudaGraphDestroy(g->graph);
+    g->pin.release(); g->dev.release();
+    delete g;
     return HB_OK;
 }

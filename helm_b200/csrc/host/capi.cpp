@@ -2,6 +2,7 @@
 #include "../../../include/helm_host.h"
 #include <algorithm>
 #include <chrono>
+#include <cstdlib>
 #include <cstring>
 #include <sstream>
 #include "eval.hpp"
@@ -191,10 +192,41 @@ int hh_session_run(hh_session* s, const hh_circuit* c, const char* inputs, int c
         const bool ready = cycles > 1 && enc->contains("READY");
         if (ready) ev.init_ready(*enc);
         const auto t1 = clk::now();
-        for (int cy = 0; cy < (cycles < 1 ? 1 : cycles); ++cy) {
-            ev.evaluate_encrypted(*enc, 1, "bool");            // the reference passes the literal 1 (helm.rs:258-263)
-            if (ready) ev.evaluate_ready(*enc);
+        // Sequential circuits: every cycle issues the same batches.  Cycle 0 runs eagerly (it also sizes the engine's scratch buffers),
+        // cycle 1 is recorded into a CUDA graph (hb_graph_begin / hb_graph_end) and that graph is launched for cycle 1 and every later
+        // cycle: one launch per cycle instead of ~3 launches + a descriptor upload per level.  HELM_NO_GRAPH=1 keeps every cycle eager.
+        hb_ctx* ctx = s->sk->ctx();
+        hb_stats_t st0{}; hb_stats(ctx, &st0);
+        const bool use_graph = cycles >= 3 && st0.n_devices == 1 && !std::getenv("HELM_NO_GRAPH");
+        hb_graph* graph = nullptr;
+        bool in_capture = false;
+        try {
+            for (int cy = 0; cy < (cycles < 1 ? 1 : cycles); ++cy) {
+                if (graph) {
+                    if (hb_graph_launch(graph) != HB_OK) throw Error(std::string("hb_graph_launch failed: ") + hb_last_error(ctx));
+                    continue;
+                }
+                const bool capture = use_graph && cy == 1;
+                if (capture) {
+                    const size_t bytes = 256 * (nl.gates.size() + 4 * nl.outputs.size()) + 1024 * (c->c->levels().size() + 4) + 65536;
+                    if (hb_graph_begin(ctx, bytes) != HB_OK) throw Error(std::string("hb_graph_begin failed: ") + hb_last_error(ctx));
+                    in_capture = true;
+                }
+                ev.evaluate_encrypted(*enc, 1, "bool");        // the reference passes the literal 1 (helm.rs:258-263)
+                if (ready) ev.evaluate_ready(*enc);
+                if (capture) {
+                    in_capture = false;
+                    if (hb_graph_end(ctx, &graph) != HB_OK) throw Error(std::string("hb_graph_end failed: ") + hb_last_error(ctx));
+                    if (hb_graph_launch(graph) != HB_OK) throw Error(std::string("hb_graph_launch failed: ") + hb_last_error(ctx));
+                }
+            }
+            if (hb_sync(ctx) != HB_OK) throw Error(std::string("hb_sync failed: ") + hb_last_error(ctx));
+        } catch (...) {
+            if (in_capture) { hb_graph* dead = nullptr; hb_graph_end(ctx, &dead); if (dead) hb_graph_destroy(dead); }   // abort the capture
+            if (graph) hb_graph_destroy(graph);
+            throw;
         }
+        if (graph) hb_graph_destroy(graph);
         const auto t2 = clk::now();
         WireValues res = ev.decrypt_outputs(*enc, verbose != 0, ready);
         if (all_wires) {                                       // every wire that was driven or is an input

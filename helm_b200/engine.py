@@ -47,7 +47,7 @@ assert SOP_DTYPE.itemsize == 40 and SOP_DTYPE.fields["in"][1] == 8 and SOP_DTYPE
 EXPORTS = ["hb_ctx_create", "hb_ctx_create_multi", "hb_ctx_destroy", "hb_last_error", "hb_set_params", "hb_load_bsk", "hb_load_ksk",
            "hb_wires_create", "hb_wires_attach", "hb_wires_destroy", "hb_ct_words", "hb_wire_stride",
            "hb_wires_device_ptr", "hb_wires_write", "hb_wires_read", "hb_wires_write_rows", "hb_wires_read_rows", "hb_wires_write_rows_async", "hb_wires_read_rows_async", "hb_io_sync", "hb_io_stream", "hb_io_fence", "hb_wires_set_trivial", "hb_eval_level", "hb_eval_shortint_ops",
-           "hb_sync", "hb_stats", "hb_stream", "hb_pbs_batch", "hb_keyswitch_batch", "hb_keyswitch_batch_noalloc",
+           "hb_sync", "hb_stats", "hb_graph_begin", "hb_graph_end", "hb_graph_launch", "hb_graph_destroy", "hb_stream", "hb_pbs_batch", "hb_keyswitch_batch", "hb_keyswitch_batch_noalloc",
            "hb_measure_fp64_peak"]
 
 _LIB = None
@@ -96,6 +96,10 @@ def lib():
         L.hb_eval_level.argtypes = [vp, vp, vp, u32]
         L.hb_eval_shortint_ops.argtypes = [vp, vp, vp, u32]
         L.hb_sync.argtypes = [vp]
+        L.hb_graph_begin.argtypes = [vp, C.c_size_t]
+        L.hb_graph_end.argtypes = [vp, C.POINTER(vp)]
+        L.hb_graph_launch.argtypes = [vp]
+        L.hb_graph_destroy.argtypes = [vp]
         L.hb_stats.argtypes = [vp, C.POINTER(HbStats)]
         L.hb_stream.restype = vp
         L.hb_stream.argtypes = [vp]
@@ -189,6 +193,21 @@ class Engine:
 
     def sync(self):
         self._ck(self.L.hb_sync(self.h), "hb_sync")
+
+    def graph_begin(self, job_bytes):
+        """records (does not run) the eval_level / eval_shortint_ops calls until graph_end(); returns nothing"""
+        self._ck(self.L.hb_graph_begin(self.h, job_bytes), "hb_graph_begin")
+
+    def graph_end(self):
+        g = C.c_void_p()
+        self._ck(self.L.hb_graph_end(self.h, C.byref(g)), "hb_graph_end")
+        return g
+
+    def graph_launch(self, g):
+        self._ck(self.L.hb_graph_launch(g), "hb_graph_launch")
+
+    def graph_destroy(self, g):
+        self.L.hb_graph_destroy(g)
 
     def io_stream(self):
         return self.L.hb_io_stream(self.h)

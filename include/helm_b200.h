@@ -150,6 +150,18 @@ typedef struct {
 hb_status hb_eval_shortint_ops(hb_ctx*, hb_wires*, const hb_sop* ops, uint32_t n_ops);
 hb_status hb_sync(hb_ctx*);
 hb_status hb_stats(hb_ctx*, hb_stats_t* out);
+/* CUDA-graph capture of a sequence of batches (a cycle of a sequential circuit issues the same batches every time; the reference
+ * re-issues every gate per cycle, src/bin/helm.rs:256-270).  Between hb_graph_begin and hb_graph_end the hb_eval_level /
+ * hb_eval_shortint_ops / hb_wires_set_trivial calls on the context are RECORDED, not executed (hb_sync is a no-op; no other entry point
+ * may be used); job_bytes bounds the descriptors of the recorded batches (~ 200 bytes per gate is ample).  The same batches must have run
+ * eagerly once before, so that the context's scratch buffers have their final size.  hb_graph_launch replays the sequence on the
+ * context's stream (asynchronous; any number of times); it fails with HB_ERR_STATE if a later, larger batch reallocated the scratch
+ * buffers the graph points into.  Single-device contexts only. */
+typedef struct hb_graph hb_graph;
+hb_status hb_graph_begin(hb_ctx*, size_t job_bytes);
+hb_status hb_graph_end(hb_ctx*, hb_graph** out);
+hb_status hb_graph_launch(hb_graph*);
+hb_status hb_graph_destroy(hb_graph*);
 /* CUDA stream of the context (cudaStream_t as void*), for callers that interleave collectives */
 void* hb_stream(hb_ctx*);
 

@@ -8,7 +8,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 TY = {"hb_status": "i32", "int32_t": "i32", "uint32_t": "u32", "uint64_t": "u64", "size_t": "usize", "double": "f64",
       "void": "c_void", "char": "c_char", "hb_ctx": "HbCtx", "hb_wires": "HbWires", "hb_params": "HbParams", "hb_gate": "HbGate",
-      "hb_sop": "HbSop", "hb_stats_t": "HbStats"}
+      "hb_sop": "HbSop", "hb_stats_t": "HbStats", "hb_graph": "HbGraph"}
 
 
 def rust_type(c):

@@ -238,3 +238,48 @@ def test_negated_input_flags_equal_explicit_not(keys_factory, engine_factory, or
         x, y, s = (int(bits[g, q]) ^ ((flags[g] >> q) & 1) for q in range(3))
         assert K.dec_bool(got[g]) == bool(_plain(E, int(ops[g]), x, y, s))
     w.close()
+
+
+def test_cuda_graph_replay_of_a_batch_sequence(keys_factory, engine_factory, oracle_mod):
+    """hb_graph_begin / hb_graph_end / hb_graph_launch: two dependent levels (a narrow one on the cluster kernel and a wide
+    one on the throughput kernels) recorded once and replayed three times on fresh inputs give, each time, the ciphertexts of the
+    eager evaluation -- i.e. of the oracle."""
+    from helm_b200 import engine as E
+    K, eng = keys_factory("toy32"), engine_factory("toy32")
+    W1, W2 = 40, 300
+    rng = np.random.default_rng(53)
+    w = eng.wires(W1 + W1 + W2)
+    ops1 = rng.integers(0, 6, size=W1).astype(np.uint8)
+    a1, b1 = rng.integers(0, W1, size=W1), rng.integers(0, W1, size=W1)
+    ops2 = rng.integers(0, 6, size=W2).astype(np.uint8)
+    a2, b2 = W1 + rng.integers(0, W1, size=W2), W1 + rng.integers(0, W1, size=W2)
+    g1 = E.make_gates(ops1, a1, b1, W1 + np.arange(W1))
+    g2 = E.make_gates(ops2, a2, b2, 2 * W1 + np.arange(W2))
+
+    def eager(cts):
+        w.write_rows(0, cts)
+        eng.eval_level(w, g1); eng.eval_level(w, g2); eng.sync()
+        out = np.zeros((W2, eng.ct_words), dtype=eng.dtype)
+        w.read_rows(2 * W1, out)
+        return out
+    inputs = [K.enc_bool_batch(rng.integers(0, 2, size=W1), 71000 + 100 * i) for i in range(4)]
+    want = [eager(c) for c in inputs]                      # also sizes the scratch buffers
+    before = eng.stats()
+    eng.graph_begin(1 << 20)
+    eng.eval_level(w, g1); eng.eval_level(w, g2); eng.sync()     # recorded, not run
+    g = eng.graph_end()
+    assert eng.stats()["pbs_count"] == before["pbs_count"]
+    for i in (1, 2, 3):
+        w.write_rows(0, inputs[i])
+        eng.graph_launch(g)
+        eng.sync()
+        out = np.zeros((W2, eng.ct_words), dtype=eng.dtype)
+        w.read_rows(2 * W1, out)
+        assert np.array_equal(out, want[i]), "replay %d differs from the eager evaluation" % i
+    assert eng.stats()["pbs_count"] - before["pbs_count"] == 3 * (W1 + W2)
+    eng.graph_destroy(g)
+    cpu = np.concatenate([inputs[1], np.zeros((W1 + W2, eng.ct_words), dtype=eng.dtype)])
+    K.bool_level(cpu, ops1, a1, b1, a1, W1 + np.arange(W1), mode=oracle_mod.EXACT)
+    K.bool_level(cpu, ops2[:16], a2[:16], b2[:16], a2[:16], 2 * W1 + np.arange(16), mode=oracle_mod.EXACT)
+    assert np.array_equal(want[1][:16], cpu[2 * W1:2 * W1 + 16])
+    w.close()
