@@ -248,8 +248,8 @@ def iscas_latency(name, device, params=PARAM_SET):
         best = secs if best is None or secs[1] < best[1] else best
     widths = circ.level_widths()
     pbs = circ.count(H.Circuit.PBS_GATES) + sum(1 for g in circ.gates() if g[1] == "mux")
-    sess.close()
     batches = (sess.stats()["levels"] - lv0) // 8          # hb_eval_level calls per evaluation: NOT / BUF folded into their consumers
+    sess.close()
     return {"netlist": name, "params": params, "levels": len(widths), "batches": int(batches), "max_width": max(widths), "pbs": pbs,
             "evaluate_ms": 1e3 * best[1], "encrypt_ms": 1e3 * best[0], "decrypt_ms": 1e3 * best[2],
             "pbs_per_s": pbs / best[1], "inputs": "all false", "outputs_verified": True}

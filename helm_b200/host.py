@@ -186,8 +186,13 @@ class Session:
         except Exception:
             pass
 
+    def _open(self):
+        if not self.h:
+            raise HostError("session is closed")
+
     def run(self, circuit, inputs=None, cycles=1, all_wires=False, verbose=False):
         """encrypt_inputs -> evaluate_encrypted x cycles -> decrypt_outputs.  Returns (values, seconds[3])."""
+        self._open()
         secs = (C.c_double * 3)()
         txt = _text(lambda b, c, n: self.L.hh_session_run(self.h, circuit.h, _fmt(inputs), cycles, int(all_wires),
                                                           int(verbose), b, c, n, secs), cap=1 << 22)
@@ -195,6 +200,7 @@ class Session:
 
     def run_arith(self, circuit, inputs=None, ptxt_type="u32", cycles=1, all_wires=False, verbose=False):
         """Arithmetic mode (reference ArithCircuit).  Returns (values, seconds[3], {"bootstraps", "batches"})."""
+        self._open()
         secs = (C.c_double * 3)()
         cnt = (C.c_uint64 * 2)()
         txt = _text(lambda b, c, n: self.L.hh_session_run_arith(self.h, circuit.h, _fmt(inputs), ptxt_type.encode(), cycles,
@@ -202,6 +208,8 @@ class Session:
         return _parse(txt), list(secs), {"bootstraps": int(cnt[0]), "batches": int(cnt[1])}
 
     def stats(self):
+        if not self.h:
+            raise HostError("session is closed")
         out = (C.c_uint64 * 4)()
         _ck(self.L.hh_session_stats(self.h, out))
         d = dict(zip(("pbs_count", "ks_count", "levels", "kernel_launches"), (int(v) for v in out)))
