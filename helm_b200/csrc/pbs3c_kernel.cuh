@@ -113,9 +113,6 @@ __global__ void __cluster_dims__(K + 1, 1, 1) __launch_bounds__(NT, 1) pbs3c_ker
     const int tr = tid / TPT, lt = tid % TPT;
     auto tsync = [&]() { if (TPT <= 32) __syncwarp(); else __syncthreads(); };
     uint32_t kphase = 0, ex_steps = 0;                // executed (non-skipped) steps so far
-    uint32_t peer_recv[K + 1], peer_bar[K + 1];       // this CTA's receive area / mbarriers as seen in CTA j's window of the cluster
-#pragma unroll
-    for (int j = 0; j <= K; ++j) { peer_recv[j] = mapa_shared(recv_addr, (uint32_t)j); peer_bar[j] = mapa_shared(rbar, (uint32_t)j); }
 
     for (int i = 0; i < n; ++i) {
         const int a = atil[i];
@@ -210,10 +207,7 @@ __global__ void __cluster_dims__(K + 1, 1, 1) __launch_bounds__(NT, 1) pbs3c_ker
         __syncthreads();
         // ---- MAC with rows (lev, r) of BSK_i: K+1 partial spectra; partial r stays, partial j goes to CTA j
         mbar_wait(kbar, kphase); kphase ^= 1u;
-        static_assert(M % NT == 0, "whole positions per thread");
-#pragma unroll
-        for (int q = 0; q < M / NT; ++q) {            // constant trip count: the positions of a thread interleave
-            const int pos = tid + q * NT;
+        for (int pos = tid; pos < M; pos += NT) {
             const int f = (pos / KB2) + KA * (pos % KB2);
             const int xa = C::addr(f % R1, (f / R1) % R2, f / (R1 * R2));
             double2 o[K + 1];
@@ -230,8 +224,8 @@ __global__ void __cluster_dims__(K + 1, 1, 1) __launch_bounds__(NT, 1) pbs3c_ker
                 if (j == r) OUT[xa] = o[j];
                 else {
                     const int slot = r < j ? r : r - 1;
-                    const uint32_t off = (uint32_t)((((size_t)buf * K + slot) * XSZ + xa) * sizeof(double2));
-                    st_async_f64x2(peer_recv[j] + off, o[j], peer_bar[j] + 8 * buf);
+                    const uint32_t dst = recv_addr + (uint32_t)((((size_t)buf * K + slot) * XSZ + xa) * sizeof(double2));
+                    st_async_f64x2(mapa_shared(dst, (uint32_t)j), o[j], mapa_shared(rbar + 8 * buf, (uint32_t)j));
                 }
             }
         }
