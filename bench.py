@@ -517,7 +517,10 @@ def main():
         io_ext = torch.cuda.ExternalStream(eng.io_stream(), device=torch.device("cuda", local)) if (world > 1 and not group) else None
         # its own communicator: NCCL serialises the collectives of one communicator, and the all-gather of step s+1's inputs must not
         # queue behind the all-gather of step s's outputs (which waits for the evaluation of step s)
-        in_group = dist.new_group() if io_ext is not None else None
+        in_group = None
+        if io_ext is not None:
+            opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)   # its kernels must get SM slots while a PBS kernel runs
+            in_group = dist.new_group(pg_options=opts)
 
         def e2e_level(s):
             # inputs in an even block, outputs in the odd block after it: consecutive steps touch disjoint rows, so the upload of step

@@ -1554,8 +1554,13 @@ extern "C" hb_status hb_keyswitch_batch_noalloc(hb_ctx* c, const void* lwe_in_de
 namespace {
 hb_status io_setup(hb_ctx* c) {
     if (c->io_stream) return HB_OK;
-    CU(c, cudaStreamCreateWithFlags(&c->io_stream, cudaStreamNonBlocking));
-    CU(c, cudaStreamCreateWithFlags(&c->io_down, cudaStreamNonBlocking));
+    // highest priority: the small repack kernels (and whatever the caller puts on the upload stream) must not queue behind the thousands of
+    // pending CTAs of a running PBS kernel, or the copy of batch s+1 only completes after batch s and nothing overlaps (measured at N = 8:
+    // 73.4 ms per step against 66.8 resident with default priority)
+    int prio_lo = 0, prio_hi = 0;
+    CU(c, cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    CU(c, cudaStreamCreateWithPriority(&c->io_stream, cudaStreamNonBlocking, prio_hi));
+    CU(c, cudaStreamCreateWithPriority(&c->io_down, cudaStreamNonBlocking, prio_hi));
     CU(c, cudaEventCreateWithFlags(&c->io_written, cudaEventDisableTiming));
     CU(c, cudaEventCreateWithFlags(&c->io_computed, cudaEventDisableTiming));
     return HB_OK;
