@@ -283,3 +283,37 @@ def test_cuda_graph_replay_of_a_batch_sequence(keys_factory, engine_factory, ora
     K.bool_level(cpu, ops2[:16], a2[:16], b2[:16], a2[:16], 2 * W1 + np.arange(16), mode=oracle_mod.EXACT)
     assert np.array_equal(want[1][:16], cpu[2 * W1:2 * W1 + 16])
     w.close()
+
+
+def test_io_stream_and_fence_order_caller_work_before_evaluation(keys_factory, engine_factory):
+    """hb_io_stream / hb_io_fence: work the caller enqueues on the upload stream after an asynchronous upload (in bench.py: the
+    all-gather of the ranks' input shares; here: a device copy of the uploaded rows into another block of an attached wire array)
+    happens before every evaluation issued after the fence."""
+    import torch
+    from helm_b200 import engine as E
+    K, eng = keys_factory("toy32"), engine_factory("toy32")
+    W = 200
+    dev = torch.device("cuda", 0)
+    wt = torch.zeros((3 * W, eng.stride), dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+    w = eng.wires(3 * W, device_ptr=wt.data_ptr())
+    io = torch.cuda.ExternalStream(eng.io_stream(), device=dev)
+    rng = np.random.default_rng(61)
+    for rep in range(3):
+        bits = rng.integers(0, 2, size=W)
+        h = torch.empty((W, eng.ct_words), dtype=torch.int32).pin_memory()
+        h.numpy().view(eng.dtype)[:] = K.enc_bool_batch(bits, 9100 + rep)
+        w.write_rows_async(0, h.numpy().view(eng.dtype))                   # block 0 <- host
+        with torch.cuda.stream(io):
+            wt[W:2 * W].copy_(wt[0:W], non_blocking=True)                  # caller work on the upload stream: block 1 <- block 0
+        eng.io_fence()
+        ops = rng.integers(0, 6, size=W).astype(np.uint8)
+        i0, i1 = rng.integers(0, W, size=W), rng.integers(0, W, size=W)
+        eng.eval_level(w, E.make_gates(ops, W + i0, W + i1, 2 * W + np.arange(W)))   # reads block 1
+        eng.sync()
+        eng.io_sync()
+        out = np.zeros((W, eng.ct_words), dtype=eng.dtype)
+        w.read_rows(2 * W, out)
+        want = np.array([_plain(E, int(o), int(bits[a]), int(bits[b]), 0) for o, a, b in zip(ops, i0, i1)], dtype=bool)
+        assert np.array_equal(K.dec_bool_batch(out), want), "repetition %d" % rep
+    w.close()
